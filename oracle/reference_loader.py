@@ -1,0 +1,64 @@
+"""ORACLE -- TEST INFRASTRUCTURE ONLY.  Imports the REAL reference modules from
+/root/reference/src (present only in the build container, never on the GPU box).
+
+Fixes applied, all documented in SURVEY.md §8(c) / Appendix D:
+  1. `transformers` -> oracle/shim/transformers (2.9.0 restatement) while importing.
+  2. src/seq_gen.py:216 `indices / V` -> `indices // V` (true division on torch>=1.5 breaks gather).
+  3. `apex` stub (src/translate.py:6), `faster_rcnn_feats` stub (src/image_model.py:9).
+Nothing from the reference is copied into the repo; files are exec'd where they lie.
+"""
+import importlib
+import os
+import sys
+import types
+
+REF_SRC = "/root/reference/src"
+SHIM = os.path.join(os.path.dirname(os.path.abspath(__file__)), "shim")
+_cache = {}
+
+
+def available():
+    return os.path.isfile(os.path.join(REF_SRC, "seq_gen.py"))
+
+
+def load():
+    """Returns a namespace with the reference modules: seq_gen, seq2seq, mass_seq2seq, bert_seq2seq."""
+    if "ns" in _cache:
+        return _cache["ns"]
+    if not available():
+        raise RuntimeError("reference sources not present (expected only in the build container)")
+    saved = {k: v for k, v in sys.modules.items() if k == "transformers" or k.startswith("transformers.")}
+    for k in saved:
+        del sys.modules[k]
+    sys.path.insert(0, REF_SRC)
+    sys.path.insert(0, SHIM)
+    try:
+        apex = types.ModuleType("apex")
+        apex.amp = types.ModuleType("apex.amp")
+        apex.amp.initialize = lambda m, **kw: m
+        sys.modules["apex"] = apex
+        sys.modules["apex.amp"] = apex.amp
+        frc = types.ModuleType("faster_rcnn_feats")
+        frc.fasterrcnn_resnet50_fpn = lambda *a, **k: None
+        sys.modules["faster_rcnn_feats"] = frc
+
+        src = open(os.path.join(REF_SRC, "seq_gen.py")).read()
+        needle = "beam_indices = indices / output.size(-1)"
+        assert src.count(needle) == 1
+        src = src.replace(needle, "beam_indices = indices // output.size(-1)")
+        seq_gen = types.ModuleType("seq_gen")
+        seq_gen.__file__ = os.path.join(REF_SRC, "seq_gen.py")
+        exec(compile(src, seq_gen.__file__, "exec"), seq_gen.__dict__)
+        sys.modules["seq_gen"] = seq_gen
+
+        ns = types.SimpleNamespace(seq_gen=seq_gen)
+        for name in ("bert_seq2seq", "seq2seq", "mass_seq2seq", "dataset"):
+            setattr(ns, name, importlib.import_module(name))
+    finally:
+        sys.path.remove(SHIM)
+        sys.path.remove(REF_SRC)
+        for k in [k for k in sys.modules if k == "transformers" or k.startswith("transformers.")]:
+            del sys.modules[k]
+        sys.modules.update(saved)
+    _cache["ns"] = ns
+    return ns
