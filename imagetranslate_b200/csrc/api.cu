@@ -1,0 +1,162 @@
+// C-ABI glue: error reporting, GEMM dispatch, the whole-step driver (include/itb.h).
+#include <cuda.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <vector>
+#include "common.cuh"
+#include "launch.h"
+
+int itb_gemm_simt(int dtype, int epi, const void* ctl, const void* A, const void* W, const float* bias, void* out,
+                  int M, int N, int K, int ldo, cudaStream_t s);
+int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const void* ctl, const float* bias, void* out,
+                int M, int N, int K, int ldo, cudaStream_t s);
+int itb_make_tmap_bf16(CUtensorMap* map, const void* base, int rows, int K, int box_rows);
+int itb_tc_pick_mt(int M);
+
+static thread_local char g_err[512] = "";
+
+void itb_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int itb_check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        itb_set_error("%s: launch failed: %s", what, cudaGetErrorString(e));
+        return -1;
+    }
+    return 0;
+}
+
+static bool use_tc(int dtype, int impl) {
+    if (impl == ITB_GEMM_SIMT) return false;
+    return dtype == ITB_BF16;      // fp32 (parity mode) always runs on the CUDA cores
+}
+
+// One linear with its cached TMA descriptors.
+struct Linear {
+    const void* W = nullptr; const float* bias = nullptr; const void* A = nullptr; void* out = nullptr;
+    int M = 0, N = 0, K = 0, ldo = 0, epi = 0;
+    bool tc = false;
+    CUtensorMap tmW, tmA;
+    int prepare(int dtype, int impl) {
+        tc = use_tc(dtype, impl);
+        if (!tc) return 0;
+        int r = itb_make_tmap_bf16(&tmW, W, N, K, 128);
+        if (r != 0) return r;
+        return itb_make_tmap_bf16(&tmA, A, M, K, itb_tc_pick_mt(M));
+    }
+    int run(int dtype, const void* ctl, cudaStream_t s) const {
+        if (tc) return itb_gemm_tc(epi, &tmW, &tmA, ctl, bias, out, M, N, K, ldo, s);
+        return itb_gemm_simt(dtype, epi, ctl, A, W, bias, out, M, N, K, ldo, s);
+    }
+};
+
+static Linear make_linear(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int ldo, int epi) {
+    Linear l;
+    l.A = A; l.W = W; l.bias = bias; l.out = out; l.M = M; l.N = N; l.K = K; l.ldo = ldo; l.epi = epi;
+    return l;
+}
+
+struct itb_decoder {
+    itb_config cfg;
+    std::vector<itb_layer> layers;
+    std::vector<Linear> qkv, o, cq, co, f1, f2;
+    Linear vocab;
+};
+
+extern "C" {
+
+int itb_abi_version(void) { return ITB_ABI_VERSION; }
+const char* itb_last_error(void) { return g_err; }
+
+int itb_linear(int dtype, int impl, int epi, const void* A, const void* W, const float* bias, void* out, int M, int N,
+               int K, int ldo, void* stream) {
+    ITB_REQUIRE(dtype == ITB_F32 || dtype == ITB_BF16, "linear: unknown dtype");
+    ITB_REQUIRE(!(impl == ITB_GEMM_TCGEN05 && dtype != ITB_BF16), "linear: tcgen05 path is bf16 only");
+    Linear l = make_linear(A, W, bias, out, M, N, K, ldo, epi);
+    int r = l.prepare(dtype, impl);
+    if (r != 0) return r;
+    return l.run(dtype, nullptr, (cudaStream_t)stream);
+}
+
+int itb_cross_kv(int dtype, int impl, const void* memory, const void* w_ckv, const float* b_ckv, void* cross_kv,
+                 int rows, int d, int L, void* stream) {
+    return itb_linear(dtype, impl, ITB_EPI_BIAS_ACT, memory, w_ckv, b_ckv, cross_kv, rows, L * 2 * d, d, L * 2 * d, stream);
+}
+
+int itb_decoder_create(const itb_config* c, itb_decoder** out) {
+    ITB_REQUIRE(c != nullptr && out != nullptr, "decoder_create: null argument");
+    ITB_REQUIRE(c->dtype == ITB_F32 || c->dtype == ITB_BF16, "decoder_create: unknown dtype");
+    ITB_REQUIRE(c->d == c->H * 64, "decoder_create: only head_dim 64 is supported (hidden = 64 * heads)");
+    ITB_REQUIRE(c->d % 64 == 0 && c->F % 64 == 0, "decoder_create: hidden and FFN sizes must be multiples of 64");
+    ITB_REQUIRE(c->beam >= 1 && c->beam <= 16, "decoder_create: beam width must be in [1,16]");
+    ITB_REQUIRE(c->B >= 1 && c->L >= 1 && c->V >= c->beam && c->S >= 1 && c->T_max >= 2, "decoder_create: bad sizes");
+    itb_decoder* d = new itb_decoder();
+    d->cfg = *c;
+    d->layers.assign(c->layers_host, c->layers_host + c->L);
+    d->cfg.layers_host = d->layers.data();
+    const int M = c->B * c->beam, D = c->d, F = c->F;
+    const int ldl = (c->V + 3) / 4 * 4;
+    int r = 0;
+    for (int l = 0; l < c->L && r == 0; ++l) {
+        const itb_layer& w = d->layers[l];
+        d->qkv.push_back(make_linear(c->x_act, w.w_qkv, w.b_qkv, c->qkv, M, 3 * D, D, 3 * D, ITB_EPI_BIAS_F32));
+        d->o.push_back(make_linear(c->ctx, w.w_o, w.b_o, c->y, M, D, D, D, ITB_EPI_BIAS_F32));
+        d->cq.push_back(make_linear(c->x_act, w.w_cq, w.b_cq, c->qkv, M, D, D, 3 * D, ITB_EPI_BIAS_F32));
+        d->co.push_back(make_linear(c->ctx, w.w_co, w.b_co, c->y, M, D, D, D, ITB_EPI_BIAS_F32));
+        d->f1.push_back(make_linear(c->x_act, w.w_1, w.b_1, c->ffn_h, M, F, D, F, ITB_EPI_BIAS_GELU_ACT));
+        d->f2.push_back(make_linear(c->ffn_h, w.w_2, w.b_2, c->y, M, D, F, D, ITB_EPI_BIAS_F32));
+        Linear* ls[6] = {&d->qkv.back(), &d->o.back(), &d->cq.back(), &d->co.back(), &d->f1.back(), &d->f2.back()};
+        for (int i = 0; i < 6 && r == 0; ++i) r = ls[i]->prepare(c->dtype, c->gemm_impl);
+    }
+    if (r == 0) {
+        d->vocab = make_linear(c->x_act, c->w_vocab, c->b_vocab, c->logits, M, c->V, D, ldl, ITB_EPI_BIAS_F32);
+        r = d->vocab.prepare(c->dtype, c->gemm_impl);
+    }
+    if (r != 0) { delete d; return r; }
+    *out = d;
+    return 0;
+}
+
+int itb_decoder_destroy(itb_decoder* dec) {
+    delete dec;
+    return 0;
+}
+
+#define ITB_TRY(x) do { int r_ = (x); if (r_ != 0) return r_; } while (0)
+
+int itb_decoder_step(itb_decoder* dec, void* stream) {
+    ITB_REQUIRE(dec != nullptr, "decoder_step: null decoder");
+    const itb_config& c = dec->cfg;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int M = c.B * c.beam, D = c.d;
+    const size_t esz = (c.dtype == ITB_BF16) ? 2 : 4;
+    ITB_TRY(itb_embed_ln(c.dtype, c.ctl, c.tokens, c.tgt_lang, c.emb_word, c.emb_pos, c.emb_type, c.emb_ln_g, c.emb_ln_b,
+                         c.ln_eps, c.x_f32, c.x_act, M, c.beam, D, c.T_max, stream));
+    for (int l = 0; l < c.L; ++l) {
+        const itb_layer& w = dec->layers[l];
+        char* kv_l = reinterpret_cast<char*>(c.kv_self) + (size_t)l * M * c.T_max * 2 * D * esz;
+        ITB_TRY(dec->qkv[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(itb_self_attention(c.dtype, c.ctl, c.qkv, kv_l, c.anc, c.ctx, M, c.beam, D, c.H, c.T_max, stream));
+        ITB_TRY(dec->o[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, w.ln1_g, w.ln1_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
+        ITB_TRY(dec->cq[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(itb_cross_attention(c.dtype, c.ctl, c.qkv, 3 * D, c.cross_kv, l, c.src_mask, c.ctx, M, c.beam, D, c.H,
+                                    c.S, c.L, stream));
+        ITB_TRY(dec->co[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, w.ln2_g, w.ln2_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
+        ITB_TRY(dec->f1[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(dec->f2[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, w.ln3_g, w.ln3_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
+    }
+    ITB_TRY(dec->vocab.run(c.dtype, c.ctl, s));
+    ITB_TRY(itb_beam_step(&c, stream));
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,288 @@
+// Fused search step: reference src/seq_gen.py:134-143,194-227 in ONE launch.
+//
+// Phase 1 (every CTA = one (row, vocab-chunk)): streams the fp32 logits ONCE (float4, coalesced),
+//   keeping per-thread online-softmax (max, sum-exp) and a sorted top-K list; warp-shuffle merge,
+//   then a block merge.  No (M,V) log-prob tensor is ever written.
+// Phase 2 (the last CTA to finish for a sentence -- atomic ticket, nobody waits): finishes
+//   log-sum-exp per row, turns the row top-K logits into candidates
+//   (score + logp) / ((size+6)/6)^alpha, handles finished / over-length rows (all-zero rows tie;
+//   deterministic order = lowest flat index), picks the sentence top-`beam`, applies the forced-PAD
+//   rewrites, and writes the new prefixes, sizes, scores, EOS flags and the ANCESTOR TABLE that
+//   replaces the KV-cache gather.  The last sentence advances the device-side step counter and
+//   evaluates the termination rule, so the host never synchronises inside the search loop.
+// HBM roofline: 4*M*V bytes read per launch.
+#include <float.h>
+#include "common.cuh"
+#include "launch.h"
+
+struct BeamArgs {
+    ItbCtl* ctl;
+    const float* logits; int ldl;
+    int B, beam, V, T_max, n_chunk, chunk, pad_id, eos_id;
+    float alpha;
+    const int* max_lens;
+    int* tokens; unsigned char* anc; float* scores; float* sizes; unsigned char* fin;
+    float* cand_val; int* cand_idx; float* chunk_max; float* chunk_sum; int* sent_counter;
+};
+
+__device__ __forceinline__ bool better(float v, int i, float bv, int bi) { return v > bv || (v == bv && i < bi); }
+
+// One warp selects the top-K of (val, idx)[0..n) in shared memory by (val desc, idx asc).
+// Entries are consumed (idx set to -1).  Results to out_val/out_idx[0..K).
+__device__ __forceinline__ void warp_select(float* val, int* idx, int n, int K, float* out_val, int* out_idx, int lane) {
+    for (int k = 0; k < K; ++k) {
+        float bv = -INFINITY; int bi = INT_MAX; int bp = -1;
+        for (int p = lane; p < n; p += 32) {
+            int i = idx[p];
+            if (i >= 0 && (bp < 0 || better(val[p], i, bv, bi))) { bv = val[p]; bi = i; bp = p; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            int op = __shfl_xor_sync(0xffffffffu, bp, o);
+            if (op >= 0 && (bp < 0 || better(ov, oi, bv, bi))) { bv = ov; bi = oi; bp = op; }
+        }
+        if (lane == 0) {
+            out_val[k] = bv; out_idx[k] = (bp >= 0) ? bi : -1;
+            if (bp >= 0) idx[bp] = -1;
+        }
+        __syncwarp();
+    }
+}
+
+template <int KT>
+__global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
+    __shared__ float s_val[8 * KT > 16 * 16 ? 8 * KT : 16 * 16];   // phase 1: per-warp lists; phase 2: row candidates
+    __shared__ int s_idx[8 * KT > 16 * 16 ? 8 * KT : 16 * 16];
+    __shared__ float s_m[8], s_s[8];
+    __shared__ float s_pool_val[32 * KT];                          // phase 2: chunk candidates of one row
+    __shared__ int s_pool_idx[32 * KT];
+    __shared__ float s_top_val[16];
+    __shared__ int s_top_idx[16];
+    __shared__ int s_src[16], s_word[16];
+    __shared__ int s_last;
+
+    ItbCtl* ctl = a.ctl;
+    if (ctl->done) return;
+    const int step = ctl->step, cur = ctl->cur, nxt = cur ^ 1;
+    const bool first = (step == 1);
+    const int M = a.B * a.beam, K = a.beam, V = a.V;
+    const int c = blockIdx.x, r = blockIdx.y, b = r / a.beam, kslot = r % a.beam;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+
+    const bool lim = (!first) && (a.max_lens[b] < step + 1);                 // seq_gen.py:138
+    const bool row_zero = (a.fin[(size_t)cur * M + r] != 0) || lim;          // :195-197
+    const bool skip = row_zero || (first && kslot != 0);                     // step 1 has one row per sentence (:146,221)
+
+    if (!skip) {
+        float v[KT]; int id[KT];
+#pragma unroll
+        for (int j = 0; j < KT; ++j) { v[j] = -INFINITY; id[j] = INT_MAX; }
+        float m = -INFINITY, s = 0.f;
+        const int lo = c * a.chunk, hi = min(V, lo + a.chunk);
+        const float* row = a.logits + (size_t)r * a.ldl;
+        for (int i = lo + tid * 4; i < hi; i += 256 * 4) {
+            float4 x4 = *reinterpret_cast<const float4*>(row + i);
+            float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                float x = xs[e];
+                if (i + e < hi) {
+                    if (x > m) { s = s * expf(m - x) + 1.f; m = x; } else { s += expf(x - m); }
+                    if (x > v[KT - 1]) {
+                        v[KT - 1] = x; id[KT - 1] = i + e;
+#pragma unroll
+                        for (int j = KT - 1; j > 0; --j) {
+                            if (v[j] > v[j - 1]) {
+                                float tv = v[j]; v[j] = v[j - 1]; v[j - 1] = tv;
+                                int ti = id[j]; id[j] = id[j - 1]; id[j - 1] = ti;
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        // warp merge of the online-softmax pairs
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float om = __shfl_xor_sync(0xffffffffu, m, o), os = __shfl_xor_sync(0xffffffffu, s, o);
+            float nm = fmaxf(m, om);
+            if (nm == -INFINITY) { s = 0.f; } else { s = s * expf(m - nm) + os * expf(om - nm); }
+            m = nm;
+        }
+        // warp-shuffle top-K merge: K rounds of "best head wins, owner pops"
+        for (int k = 0; k < K; ++k) {
+            float bv = v[0]; int bi = id[0];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (better(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+            }
+            if (bi == id[0] && bi != INT_MAX) {
+#pragma unroll
+                for (int j = 0; j < KT - 1; ++j) { v[j] = v[j + 1]; id[j] = id[j + 1]; }
+                v[KT - 1] = -INFINITY; id[KT - 1] = INT_MAX;
+            }
+            if (lane == 0) { s_val[w * KT + k] = bv; s_idx[w * KT + k] = (bi == INT_MAX) ? -1 : bi; }
+        }
+        if (lane == 0) {
+            for (int k = K; k < KT; ++k) { s_val[w * KT + k] = -INFINITY; s_idx[w * KT + k] = -1; }
+            s_m[w] = m; s_s[w] = s;
+        }
+        __syncthreads();
+        if (w == 0) {
+            const size_t o = ((size_t)r * a.n_chunk + c) * KT;
+            warp_select(s_val, s_idx, 8 * KT, K, a.cand_val + o, a.cand_idx + o, lane);
+            if (lane == 0) {
+                float mm = -INFINITY, ss = 0.f;
+                for (int j = 0; j < 8; ++j) mm = fmaxf(mm, s_m[j]);
+                for (int j = 0; j < 8; ++j) if (s_m[j] != -INFINITY) ss += s_s[j] * expf(s_m[j] - mm);
+                a.chunk_max[(size_t)r * a.n_chunk + c] = mm;
+                a.chunk_sum[(size_t)r * a.n_chunk + c] = ss;
+            }
+        }
+    }
+
+    // ---- ticket: the last CTA of this sentence runs phase 2 ----
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        int t = atomicAdd(&a.sent_counter[b], 1);
+        s_last = (t == a.beam * a.n_chunk - 1);
+        if (s_last) __threadfence();
+    }
+    __syncthreads();
+    if (!s_last) return;
+
+    // ---------------------------------- phase 2 (one CTA per sentence) ----------------------------------
+    const int nrows = first ? 1 : K;
+    float* rc_val = s_val;      // [nrows][K] row candidates (sentence-level values)
+    int* rc_idx = s_idx;
+    for (int kr = 0; kr < nrows; ++kr) {
+        const int rr = b * a.beam + kr;
+        const float sc = a.scores[(size_t)cur * M + rr];
+        float lp = 1.f;
+        if (K > 1) lp = powf((a.sizes[(size_t)cur * M + rr] + 6.0f) / 6.0f, a.alpha);     // seq_gen.py:43
+        const bool rz = (a.fin[(size_t)cur * M + rr] != 0) || lim;
+        __syncthreads();
+        if (rz) {
+            // whole row is 0 => V exact ties at (score + 0)/lp; lowest flat index first
+            if (tid < K) {
+                float cv = sc + 0.0f;
+                if (K > 1) cv = cv / lp;
+                rc_val[kr * K + tid] = cv;
+                rc_idx[kr * K + tid] = kr * V + tid;
+            }
+        } else {
+            const int n = a.n_chunk * KT;
+            for (int i = tid; i < n; i += blockDim.x) {
+                s_pool_val[i] = __ldcg(a.cand_val + (size_t)rr * n + i);
+                s_pool_idx[i] = __ldcg(a.cand_idx + (size_t)rr * n + i);
+            }
+            __syncthreads();
+            if (w == 0) {
+                float mm = -INFINITY, ss = 0.f;
+                for (int j = lane; j < a.n_chunk; j += 32) mm = fmaxf(mm, __ldcg(a.chunk_max + (size_t)rr * a.n_chunk + j));
+                mm = warp_max(mm);
+                for (int j = lane; j < a.n_chunk; j += 32) {
+                    float cm = __ldcg(a.chunk_max + (size_t)rr * a.n_chunk + j);
+                    if (cm != -INFINITY) ss += __ldcg(a.chunk_sum + (size_t)rr * a.n_chunk + j) * expf(cm - mm);
+                }
+                ss = warp_sum(ss);
+                const float logz = logf(ss);
+                warp_select(s_pool_val, s_pool_idx, n, K, s_top_val, s_top_idx, lane);
+                if (lane < K) {
+                    // log_softmax as ATen computes it: (x - max) - log(sum exp(x - max))   (seq_gen.py:194)
+                    float lpz = (s_top_val[lane] - mm) - logz;
+                    float cv = sc + lpz;                                                    // :199 / :201
+                    if (K > 1) cv = cv / lp;
+                    rc_val[kr * K + lane] = cv;
+                    rc_idx[kr * K + lane] = kr * V + s_top_idx[lane];
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (w == 0) {
+        warp_select(rc_val, rc_idx, nrows * K, K, s_top_val, s_top_idx, lane);              // :203
+        if (lane < K) {
+            int idx = s_top_idx[lane];
+            if (!first) {
+                if (lim) idx = a.pad_id;                                                    // :207
+                if (a.fin[(size_t)cur * M + b * a.beam + lane] != 0) idx = a.pad_id;        // :213 (new slot, old flag)
+            }
+            const int src = idx / V, word = idx % V;                                        // :216, :223
+            s_src[lane] = src; s_word[lane] = word;
+            const int rn = b * a.beam + lane, ro = b * a.beam + src;
+            a.scores[(size_t)nxt * M + rn] = s_top_val[lane];                               // :227
+            a.sizes[(size_t)nxt * M + rn] = a.sizes[(size_t)cur * M + ro] + ((word != a.pad_id) ? 1.0f : 0.0f);   // :226
+            unsigned char f = (a.fin[(size_t)cur * M + ro] != 0 || word == a.eos_id) ? 1 : 0;
+            a.fin[(size_t)nxt * M + rn] = f;
+            unsigned nf = __ballot_sync(__activemask(), f != 0);
+            if (lane == 0) atomicAdd(&ctl->fin_rows, __popc(nf));
+        }
+    }
+    __syncthreads();
+    // new prefixes (:217-224) and ancestor table (replaces the KV gather)
+    for (int j = 0; j < K; ++j) {
+        const int src = s_src[j];
+        const int* told = a.tokens + ((size_t)cur * M + b * a.beam + src) * a.T_max;
+        int* tnew = a.tokens + ((size_t)nxt * M + b * a.beam + j) * a.T_max;
+        const unsigned char* aold = a.anc + ((size_t)cur * M + b * a.beam + src) * a.T_max;
+        unsigned char* anew = a.anc + ((size_t)nxt * M + b * a.beam + j) * a.T_max;
+        for (int p = tid; p < step; p += blockDim.x) {
+            tnew[p] = told[p];
+            anew[p] = (p == step - 1) ? (unsigned char)src : aold[p];
+        }
+        if (tid == 0) tnew[step] = s_word[j];
+    }
+    __syncthreads();
+    if (tid == 0) {
+        a.sent_counter[b] = 0;
+        __threadfence();
+        int t = atomicAdd(&ctl->sent_done, 1);
+        if (t == a.B - 1) {
+            __threadfence();
+            int total_fin = atomicAdd(&ctl->fin_rows, 0);
+            ctl->steps_run = step;
+            ctl->step = step + 1;
+            ctl->cur = nxt;
+            ctl->fin_rows = 0;
+            ctl->sent_done = 0;
+            ctl->done = (total_fin == M || step + 1 >= ctl->max_len) ? 1 : 0;                // :131,134
+        }
+    }
+}
+
+static int kt_for(int beam) { return beam <= 4 ? 4 : (beam <= 8 ? 8 : 16); }
+
+extern "C" {
+
+int itb_topk_capacity(int beam) { return kt_for(beam); }
+
+int itb_beam_step(const itb_config* c, void* stream) {
+    ITB_REQUIRE(c->beam >= 1 && c->beam <= 16, "beam_step: beam width must be in [1,16]");
+    ITB_REQUIRE(c->V >= c->beam, "beam_step: vocabulary smaller than the beam");
+    ITB_REQUIRE(c->n_chunk >= 1 && c->n_chunk <= 32, "beam_step: n_chunk must be in [1,32]");
+    BeamArgs a;
+    a.ctl = reinterpret_cast<ItbCtl*>(c->ctl);
+    a.logits = c->logits; a.ldl = (c->V + 3) / 4 * 4;
+    a.B = c->B; a.beam = c->beam; a.V = c->V; a.T_max = c->T_max; a.n_chunk = c->n_chunk;
+    a.chunk = (((c->V + c->n_chunk - 1) / c->n_chunk) + 3) / 4 * 4;
+    a.pad_id = c->pad_id; a.eos_id = c->eos_id; a.alpha = c->len_alpha;
+    a.max_lens = c->max_lens; a.tokens = c->tokens; a.anc = c->anc; a.scores = c->scores; a.sizes = c->sizes;
+    a.fin = c->fin; a.cand_val = c->cand_val; a.cand_idx = c->cand_idx; a.chunk_max = c->chunk_max;
+    a.chunk_sum = c->chunk_sum; a.sent_counter = c->sent_counter;
+    dim3 grid(c->n_chunk, c->B * c->beam);
+    cudaStream_t s = (cudaStream_t)stream;
+    switch (kt_for(c->beam)) {
+        case 4: beam_step_kernel<4><<<grid, 256, 0, s>>>(a); break;
+        case 8: beam_step_kernel<8><<<grid, 256, 0, s>>>(a); break;
+        default: beam_step_kernel<16><<<grid, 256, 0, s>>>(a); break;
+    }
+    return itb_check_launch("beam_step");
+}
+
+}  // extern "C"

@@ -1,0 +1,59 @@
+// Shared device helpers for the ImageTranslate B200 decode path (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+#define ITB_WARP 32
+
+// Device-resident control block shared by every kernel of a decode call.  All step kernels
+// read `step`/`done` from here so that ONE captured CUDA graph can be replayed for every
+// step, and so that steps enqueued past termination are exact no-ops
+// (termination rule: /root/reference/src/seq_gen.py:134-136).
+struct ItbCtl {
+    int step;        // current 1-based step index i of seq_gen.py:131 (the token consumed is at position i-1)
+    int done;        // 1 once every row of the batch holds an EOS (checked before each step, like :134)
+    int steps_run;   // number of steps actually executed
+    int cur;         // ping-pong parity of the token / ancestor tables
+    int fin_rows;    // rows (over the whole batch) whose prefix holds an EOS
+    int sent_done;   // sentences that finished the merge phase of the current step
+    int max_len;     // loop bound of :131 (steps run for i in [1, max_len))
+    int pad_;
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Block-wide sum for blockDim.x <= 1024; `red` is >= 32 floats of shared memory.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) red[w] = v;
+    __syncthreads();
+    float t = (threadIdx.x < nw) ? red[threadIdx.x] : 0.f;
+    if (w == 0) {
+        t = warp_sum(t);
+        if (lane == 0) red[0] = t;
+    }
+    __syncthreads();
+    return red[0];
+}
+
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// exact (erf) GELU, as HF "gelu" (transformers 2.9.0 BertIntermediate)
+__device__ __forceinline__ float gelu_erf(float x) { return x * 0.5f * (1.0f + erff(x * 0.70710678118654752440f)); }

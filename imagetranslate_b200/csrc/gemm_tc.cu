@@ -1,0 +1,300 @@
+// tcgen05 / TMEM / TMA bf16 GEMM for the decoder linears (sm_100a):
+//     out[m][n] = epi( sum_k A[m][k] * W[n][k] + bias[n] ),   A = activations [M][K], W = nn.Linear weight [N][K]
+//
+// Decode-shaped problem: M (rows = sentences*beam) is small (60..1000) while N*K is the whole weight
+// matrix, so the kernel is WEIGHT-STREAMING and HBM-bound for M below the ridge (~250 rows).  Hence
+// "swap-AB": the weight tile is the UMMA A operand (128 weight rows -> 128 TMEM lanes) and the
+// activation rows are the UMMA N dimension (MT = 32..256 columns), so small M does not waste the
+// 128-row MMA atom and every weight byte is read from HBM exactly once.
+//
+//   warp 0   TMA producer  : cp.async.bulk.tensor 2D (SWIZZLE_128B) W[128x64] + A[MTx64] per stage
+//   warp 1   MMA issuer    : one thread, 4 x tcgen05.mma (K=16) per stage, fp32 accumulators in TMEM
+//   warp 2   TMEM allocator
+//   warps 4-7 epilogue     : tcgen05.ld 32x32b -> +bias (-> GELU) -> coalesced global stores
+// Persistent CTAs (grid = #SMs) walk the tile list; TMEM accumulators are double-buffered so the
+// epilogue of tile i overlaps the MMAs/loads of tile i+1.
+#include <cuda.h>
+#include "common.cuh"
+#include "launch.h"
+
+#define TC_BN 128          // weight rows per tile (UMMA M)
+#define TC_BK 64           // K per stage: 64 bf16 = one 128-byte swizzle row
+#define TC_THREADS 256
+#define TC_SPIN_LIMIT (1u << 28)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done = 0, spins = 0;
+    const uint32_t addr = smem_u32(bar);
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (done) break;
+        if (++spins > TC_SPIN_LIMIT) __trap();     // a protocol bug must fault, never hang the GPU
+    }
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]; kind::f16 covers bf16 inputs with fp32 accumulation.
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accum) : "memory");
+}
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (sm_100 format: version=1 at bit 46, layout type 2 at bit 61).
+// Rows are 128 bytes; 8-row groups are 1024 bytes apart (SBO); LBO unused for swizzled K-major.
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)(1024u >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+template <int MT> struct TcCfg {
+    static constexpr int kStageBytes = TC_BN * TC_BK * 2 + MT * TC_BK * 2;
+    static constexpr int kStagesRaw = (200 * 1024) / kStageBytes;
+    static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+    static constexpr int kTmemCols = (2 * MT) < 32 ? 32 : (2 * MT);            // power of two for MT in {32,64,128,256}
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+template <int MT, int EPI>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
+               const ItbCtl* __restrict__ ctl, const float* __restrict__ bias, void* __restrict__ out, int M, int N,
+               int K, int ldo) {
+    using Cfg = TcCfg<MT>;
+    extern __shared__ uint8_t smem_raw[];
+    if (ctl != nullptr && ctl->done) return;           // uniform early-out, before any barrier / TMEM allocation
+
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem_w = smem;                                           // [stages][128][64] bf16, 1024-aligned
+    uint8_t* smem_a = smem + Cfg::kStages * (TC_BN * TC_BK * 2);      // [stages][MT][64] bf16, 1024-aligned
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + Cfg::kStages;
+    uint64_t* tfull = bars + 2 * Cfg::kStages;
+    uint64_t* tempty = tfull + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_tiles = (N + TC_BN - 1) / TC_BN, m_tiles = (M + MT - 1) / MT;
+    const int total = n_tiles * m_tiles, KB = K / TC_BK;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmW)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < Cfg::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"((uint32_t)Cfg::kTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const int nt = t / m_tiles, mt = t % m_tiles;
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    mbar_expect_tx(&full[stage], Cfg::kStageBytes);
+                    tma_load_2d(smem_w + stage * (TC_BN * TC_BK * 2), &tmW, kb * TC_BK, nt * TC_BN, &full[stage]);
+                    tma_load_2d(smem_a + stage * (MT * TC_BK * 2), &tmA, kb * TC_BK, mt * MT, &full[stage]);
+                    if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // instruction descriptor: D=f32 (bit 4), A=B=bf16 (bits 7, 10), both K-major, N=MT (>>3 @17), M=128 (>>4 @24)
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(MT >> 3) << 17) | ((uint32_t)(TC_BN >> 4) << 24);
+            uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                mbar_wait(&tempty[as], aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * MT;
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint64_t dw = make_sw128_desc(smem_u32(smem_w + stage * (TC_BN * TC_BK * 2)));
+                    const uint64_t da = make_sw128_desc(smem_u32(smem_a + stage * (MT * TC_BK * 2)));
+#pragma unroll
+                    for (int k = 0; k < TC_BK / 16; ++k)       // +32 bytes (>>4 = 2) per K=16 slice inside the swizzle row
+                        umma_bf16(d_tmem, dw + 2 * k, da + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                    umma_commit(&empty[stage]);                 // frees the smem stage when the MMAs retire
+                    if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tfull[as]);                        // accumulator ready for the epilogue
+                if (++as == 2) { as = 0; aphase ^= 1; }
+            }
+        }
+    } else if (warp >= 4) {
+        const int q = warp & 3;                                 // TMEM lane quarter this warp may access
+        uint32_t as = 0, aphase = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            const int nt = t / m_tiles, mt = t % m_tiles;
+            mbar_wait(&tfull[as], aphase);
+            tc_fence_after();
+            const int n = nt * TC_BN + q * 32 + lane;
+            const float bv = (n < N && bias != nullptr) ? bias[n] : 0.f;
+#pragma unroll 1
+            for (int c0 = 0; c0 < MT; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * MT + c0, v);
+                const int mbase = mt * MT + c0;
+                if (n < N) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int m = mbase + j;
+                        if (m < M) {
+                            float x = __uint_as_float(v[j]) + bv;
+                            if (EPI == ITB_EPI_BIAS_F32) reinterpret_cast<float*>(out)[(size_t)m * ldo + n] = x;
+                            else {
+                                if (EPI == ITB_EPI_BIAS_GELU_ACT) x = gelu_erf(x);
+                                reinterpret_cast<__nv_bfloat16*>(out)[(size_t)m * ldo + n] = __float2bfloat16_rn(x);
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&tempty[as]);
+            if (++as == 2) { as = 0; aphase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)Cfg::kTmemCols) : "memory");
+    }
+}
+
+// ------------------------------------------------ host side ------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+    static PFN_encodeTiled fn = nullptr;
+    if (fn == nullptr) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_encodeTiled>(p);
+    }
+    return fn;
+}
+
+// 2-D bf16 row-major [rows][K] tensor, box = [box_rows][64], 128-byte swizzle, OOB rows read as zero.
+int itb_make_tmap_bf16(CUtensorMap* map, const void* base, int rows, int K, int box_rows) {
+    PFN_encodeTiled enc = get_encode();
+    if (enc == nullptr) { itb_set_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)"); return -3; }
+    cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)K * 2};
+    cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { itb_set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%d K=%d box=%d)", (int)r, rows, K, box_rows); return -3; }
+    return 0;
+}
+
+int itb_tc_pick_mt(int M) { return M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256)); }
+
+static int num_sms() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+template <int MT, int EPI>
+static int launch_tc(const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCtl* ctl, const float* bias, void* out,
+                     int M, int N, int K, int ldo, cudaStream_t s) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<MT>::kSmemBytes);
+        if (e != cudaSuccess) { itb_set_error("gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return -1; }
+        attr_set = true;
+    }
+    const int total = ((N + TC_BN - 1) / TC_BN) * ((M + MT - 1) / MT);
+    const int grid = total < num_sms() ? total : num_sms();
+    gemm_tc_kernel<MT, EPI><<<grid, TC_THREADS, TcCfg<MT>::kSmemBytes, s>>>(tmW, tmA, ctl, bias, out, M, N, K, ldo);
+    return itb_check_launch("gemm_tc");
+}
+
+template <int MT>
+static int launch_tc_epi(int epi, const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCtl* ctl, const float* bias,
+                         void* out, int M, int N, int K, int ldo, cudaStream_t s) {
+    if (epi == ITB_EPI_BIAS_F32) return launch_tc<MT, ITB_EPI_BIAS_F32>(tmW, tmA, ctl, bias, out, M, N, K, ldo, s);
+    if (epi == ITB_EPI_BIAS_GELU_ACT) return launch_tc<MT, ITB_EPI_BIAS_GELU_ACT>(tmW, tmA, ctl, bias, out, M, N, K, ldo, s);
+    return launch_tc<MT, ITB_EPI_BIAS_ACT>(tmW, tmA, ctl, bias, out, M, N, K, ldo, s);
+}
+
+// tmW: [N][K] box 128 rows; tmA: [M][K] box itb_tc_pick_mt(M) rows.
+int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const void* ctl, const float* bias, void* out,
+                int M, int N, int K, int ldo, cudaStream_t s) {
+    ITB_REQUIRE(K % TC_BK == 0 && K >= TC_BK, "linear(tcgen05): K must be a multiple of 64");
+    const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
+    switch (itb_tc_pick_mt(M)) {
+        case 32: return launch_tc_epi<32>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, s);
+        case 64: return launch_tc_epi<64>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, s);
+        case 128: return launch_tc_epi<128>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, s);
+        default: return launch_tc_epi<256>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, s);
+    }
+}

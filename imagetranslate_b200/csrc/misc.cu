@@ -1,0 +1,179 @@
+// Embedding + LayerNorm, residual + LayerNorm, state init, output extraction.
+// HBM-bound row kernels: one CTA per row, float4 accesses, fp32 statistics.
+#include "common.cuh"
+#include "launch.h"
+
+// LayerNorm over `d` values held in shared memory `row`; writes f32 + act copies.
+template <typename TA>
+__device__ __forceinline__ void ln_write(const float* row, int d, const float* __restrict__ g,
+                                         const float* __restrict__ b, float eps, float* __restrict__ of,
+                                         TA* __restrict__ oa, float* red) {
+    float s = 0.f;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) s += row[i];
+    float mean = block_sum(s, red) / (float)d;
+    float v = 0.f;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) { float t = row[i] - mean; v += t * t; }
+    float var = block_sum(v, red) / (float)d;
+    float rstd = rsqrtf(var + eps);
+    for (int i = threadIdx.x; i < d; i += blockDim.x) {
+        float o = (row[i] - mean) * rstd * g[i] + b[i];
+        of[i] = o;
+        oa[i] = from_f32<TA>(o);
+    }
+}
+
+template <typename TA>
+__global__ void __launch_bounds__(256) embed_ln_kernel(const ItbCtl* __restrict__ ctl, const int* __restrict__ tokens,
+                                                       const int* __restrict__ tgt_lang, const float* __restrict__ word,
+                                                       const float* __restrict__ pos, const float* __restrict__ type,
+                                                       const float* __restrict__ g, const float* __restrict__ b, float eps,
+                                                       float* __restrict__ x_f32, TA* __restrict__ x_act, int M, int beam,
+                                                       int d, int T_max) {
+    extern __shared__ float sm[];
+    float* row = sm;
+    float* red = sm + d;
+    if (ctl->done) return;
+    const int r = blockIdx.x;
+    const int p = ctl->step - 1;                     // 0-based position of the token consumed this step
+    const int tok = tokens[((size_t)ctl->cur * M + r) * T_max + p];
+    const int lang = tgt_lang[r / beam];
+    const float4* w4 = reinterpret_cast<const float4*>(word + (size_t)tok * d);
+    const float4* p4 = reinterpret_cast<const float4*>(pos + (size_t)p * d);
+    const float4* t4 = reinterpret_cast<const float4*>(type + (size_t)lang * d);
+    for (int i = threadIdx.x; i < d / 4; i += blockDim.x) {
+        float4 a = w4[i], c = p4[i], e = t4[i];
+        row[4 * i + 0] = a.x + c.x + e.x;
+        row[4 * i + 1] = a.y + c.y + e.y;
+        row[4 * i + 2] = a.z + c.z + e.z;
+        row[4 * i + 3] = a.w + c.w + e.w;
+    }
+    __syncthreads();
+    ln_write<TA>(row, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, red);
+}
+
+template <typename TA>
+__global__ void __launch_bounds__(256) add_ln_kernel(const ItbCtl* __restrict__ ctl, const float* __restrict__ y,
+                                                     const float* __restrict__ g, const float* __restrict__ b, float eps,
+                                                     float* __restrict__ x_f32, TA* __restrict__ x_act, int M, int d) {
+    extern __shared__ float sm[];
+    float* row = sm;
+    float* red = sm + d;
+    if (ctl != nullptr && ctl->done) return;
+    const int r = blockIdx.x;
+    const float4* y4 = reinterpret_cast<const float4*>(y + (size_t)r * d);
+    const float4* x4 = reinterpret_cast<const float4*>(x_f32 + (size_t)r * d);
+    for (int i = threadIdx.x; i < d / 4; i += blockDim.x) {
+        float4 a = y4[i], c = x4[i];
+        row[4 * i + 0] = a.x + c.x;
+        row[4 * i + 1] = a.y + c.y;
+        row[4 * i + 2] = a.z + c.z;
+        row[4 * i + 3] = a.w + c.w;
+    }
+    __syncthreads();
+    ln_write<TA>(row, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, red);
+}
+
+// seq_gen.py:109-123: prefix = first token in every slot, scores 0, sizes 0; ancestors = own slot.
+__global__ void init_state_kernel(ItbCtl* ctl, int* tokens, unsigned char* anc, float* scores, float* sizes,
+                                  unsigned char* fin, int* sent_counter, const int* __restrict__ first_tokens, int B,
+                                  int beam, int T_max, int eos, int max_len) {
+    const int M = B * beam;
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = gridDim.x * blockDim.x;
+    for (size_t i = tid; i < (size_t)2 * M * T_max; i += n) {
+        int r = (int)((i / T_max) % M);
+        int p = (int)(i % T_max);
+        tokens[i] = (p == 0) ? first_tokens[r / beam] : 0;
+        anc[i] = (unsigned char)(r % beam);
+    }
+    int fin_rows = 0;
+    for (int i = tid; i < 2 * M; i += n) {
+        scores[i] = 0.f;
+        sizes[i] = 0.f;
+        fin[i] = (first_tokens[(i % M) / beam] == eos) ? 1 : 0;
+    }
+    for (int i = tid; i < B; i += n) sent_counter[i] = 0;
+    if (tid == 0) {
+        for (int r = 0; r < M; ++r) fin_rows += (first_tokens[r / beam] == eos) ? 1 : 0;
+        ctl->step = 1;
+        ctl->steps_run = 0;
+        ctl->cur = 0;
+        ctl->fin_rows = 0;                           // accumulator of the NEXT state's EOS rows (beam kernel)
+        ctl->sent_done = 0;
+        ctl->max_len = max_len;
+        // seq_gen.py:131-136: loop body runs for i in [1, max_len) unless every row already holds EOS
+        ctl->done = (max_len <= 1 || fin_rows == M) ? 1 : 0;
+    }
+}
+
+// seq_gen.py:229-231 + :6-24 : slot 0, cut before first EOS else at max_lens (clamped to the row length).
+__global__ void finalize_kernel(const ItbCtl* __restrict__ ctl, const int* __restrict__ tokens,
+                                const int* __restrict__ max_lens, int eos, int* __restrict__ out_tokens,
+                                int* __restrict__ out_len, int* __restrict__ out_len_full, int B, int beam, int T_max) {
+    const int b = blockIdx.x;
+    const int M = B * beam;
+    const int n_tok = ctl->steps_run + 1;
+    const int* src = tokens + ((size_t)ctl->cur * M + (size_t)b * beam) * T_max;
+    __shared__ int first_eos;
+    if (threadIdx.x == 0) first_eos = 0x7fffffff;
+    __syncthreads();
+    for (int p = threadIdx.x; p < T_max; p += blockDim.x) {
+        int t = (p < n_tok) ? src[p] : 0;
+        out_tokens[(size_t)b * T_max + p] = t;
+        if (p < n_tok && t == eos) atomicMin(&first_eos, p);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int len = (first_eos != 0x7fffffff) ? first_eos : min(max_lens[b], n_tok);
+        out_len[b] = len;
+        out_len_full[b] = n_tok;
+    }
+}
+
+extern "C" {
+
+int itb_embed_ln(int dtype, const itb_ctl* ctl, const int* tokens, const int* tgt_lang, const float* word,
+                 const float* pos, const float* type, const float* g, const float* b, float eps, float* x_f32,
+                 void* x_act, int M, int beam, int d, int T_max, void* stream) {
+    ITB_REQUIRE(d % 4 == 0 && M > 0, "embed_ln: d must be a multiple of 4");
+    size_t smem = (d + 32) * sizeof(float);
+    cudaStream_t s = (cudaStream_t)stream;
+    const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
+    if (dtype == ITB_BF16)
+        embed_ln_kernel<__nv_bfloat16><<<M, 256, smem, s>>>(c, tokens, tgt_lang, word, pos, type, g, b, eps, x_f32,
+                                                            (__nv_bfloat16*)x_act, M, beam, d, T_max);
+    else
+        embed_ln_kernel<float><<<M, 256, smem, s>>>(c, tokens, tgt_lang, word, pos, type, g, b, eps, x_f32,
+                                                    (float*)x_act, M, beam, d, T_max);
+    return itb_check_launch("embed_ln");
+}
+
+int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, const float* g, const float* b, float eps,
+               float* x_f32, void* x_act, int M, int d, void* stream) {
+    ITB_REQUIRE(d % 4 == 0 && M > 0, "add_ln: d must be a multiple of 4");
+    size_t smem = (d + 32) * sizeof(float);
+    cudaStream_t s = (cudaStream_t)stream;
+    const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
+    if (dtype == ITB_BF16)
+        add_ln_kernel<__nv_bfloat16><<<M, 256, smem, s>>>(c, y, g, b, eps, x_f32, (__nv_bfloat16*)x_act, M, d);
+    else
+        add_ln_kernel<float><<<M, 256, smem, s>>>(c, y, g, b, eps, x_f32, (float*)x_act, M, d);
+    return itb_check_launch("add_ln");
+}
+
+int itb_init_state(const itb_config* c, const int* first_tokens, int max_len, void* stream) {
+    ITB_REQUIRE(max_len <= c->T_max, "init_state: max_len exceeds T_max");
+    init_state_kernel<<<64, 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<ItbCtl*>(c->ctl), c->tokens, c->anc, c->scores, c->sizes, c->fin, c->sent_counter,
+        first_tokens, c->B, c->beam, c->T_max, c->eos_id, max_len);
+    return itb_check_launch("init_state");
+}
+
+int itb_finalize(const itb_ctl* ctl, const int* tokens, const int* max_lens, int eos, int* out_tokens, int* out_len,
+                 int* out_len_full, int B, int beam, int T_max, void* stream) {
+    finalize_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(reinterpret_cast<const ItbCtl*>(ctl), tokens, max_lens, eos,
+                                                         out_tokens, out_len, out_len_full, B, beam, T_max);
+    return itb_check_launch("finalize");
+}
+
+}  // extern "C"

@@ -1,0 +1,146 @@
+/* itb.h -- C ABI of the B200-native ImageTranslate beam-search decode path.
+ *
+ * The reference (rasoolims/ImageTranslate) is pure Python: it has no FFI / plugin
+ * registry, its boundary for this path is the Python class
+ * `BeamDecoder` (reference src/seq_gen.py:27-48).  This header is therefore the
+ * boundary a maintainer binds with ctypes; every entry point
+ * names the reference lines whose arithmetic it replaces.
+ *
+ * Conventions: plain pointers and sizes only (no torch types); every pointer is a
+ * DEVICE pointer unless its name ends in `_host`; `stream` is a cudaStream_t passed
+ * as void*; functions only ENQUEUE work (no sync, no allocation of device memory)
+ * and return 0 on success or a negative code, with text from itb_last_error().
+ * Matrices are row-major; "act" means the compute dtype of the decoder
+ * (ITB_F32: float, ITB_BF16: __nv_bfloat16); linear weights are [out][in] exactly
+ * as torch.nn.Linear stores them (HF BertSelfAttention.query.weight etc.).
+ */
+#ifndef ITB_H_
+#define ITB_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ITB_ABI_VERSION 1
+enum { ITB_F32 = 0, ITB_BF16 = 1 };
+enum { ITB_GEMM_AUTO = 0, ITB_GEMM_SIMT = 1, ITB_GEMM_TCGEN05 = 2 };
+/* GEMM epilogues */
+enum { ITB_EPI_BIAS_F32 = 0,      /* out f32  = acc + bias                                  */
+       ITB_EPI_BIAS_GELU_ACT = 1, /* out act  = gelu_erf(acc + bias)  (HF BertIntermediate) */
+       ITB_EPI_BIAS_ACT = 2 };    /* out act  = acc + bias                                  */
+
+/* Control block living in device memory (see csrc/common.cuh for field meaning). */
+typedef struct { int step, done, steps_run, cur, fin_rows, sent_done, max_len, pad_; } itb_ctl;
+
+/* One decoder layer of HF-2.9.0 BertLayer(is_decoder=True). */
+typedef struct {
+  const void* w_qkv;  const float* b_qkv;   /* [3d][d]: attention.self.{query,key,value} stacked      */
+  const void* w_o;    const float* b_o;     /* attention.output.dense                                   */
+  const float* ln1_g; const float* ln1_b;   /* attention.output.LayerNorm                               */
+  const void* w_cq;   const float* b_cq;    /* crossattention.self.query                                */
+  const void* w_co;   const float* b_co;    /* crossattention.output.dense                              */
+  const float* ln2_g; const float* ln2_b;   /* crossattention.output.LayerNorm                          */
+  const void* w_1;    const float* b_1;     /* intermediate.dense [F][d]                                */
+  const void* w_2;    const float* b_2;     /* output.dense [d][F]                                      */
+  const float* ln3_g; const float* ln3_b;   /* output.LayerNorm                                         */
+} itb_layer;
+
+/* Everything one decode call needs.  Filled by the host (imagetranslate_b200/engine.py). */
+typedef struct {
+  int dtype, gemm_impl;
+  int B, beam, d, H, F, L, V, S, T_max;     /* M = B*beam rows; S = memory length; T_max = max tokens/row */
+  int pad_id, eos_id, n_chunk, reserved0;
+  float len_alpha, ln_eps;                  /* length-penalty exponent (seq_gen.py:43); LayerNorm eps     */
+  /* decoder embeddings (f32 tables) -- HF BertEmbeddings */
+  const float *emb_word, *emb_pos, *emb_type, *emb_ln_g, *emb_ln_b;
+  const itb_layer* layers_host;             /* HOST array of L entries (copied at create)                 */
+  const void* w_vocab; const float* b_vocab;/* BertOutputLayer.layer (bert_seq2seq.py:6-12) [V][d], [V]   */
+  /* per-call inputs */
+  const int* tgt_lang;                      /* [B] token-type id of the target language (seq_gen.py:148)  */
+  const int* max_lens;                      /* [B] (seq_gen.py:119-121)                                    */
+  const unsigned char* src_mask;            /* [B][S] 1 = attend, or NULL (image memory, seq_gen.py:153)   */
+  const void* cross_kv;                     /* act [B][S][L][2][d]: cross K,V of every layer                */
+  /* search state */
+  itb_ctl* ctl;
+  int* tokens;                              /* [2][M][T_max]   ping-pong prefixes                          */
+  unsigned char* anc;                       /* [2][M][T_max]   beam slot that physically holds position p  */
+  float* scores;                            /* [2][M]                                                      */
+  float* sizes;                             /* [2][M]                                                      */
+  unsigned char* fin;                       /* [2][M]          prefix holds EOS                            */
+  void* kv_self;                            /* act [L][M][T_max][2][d]                                     */
+  /* scratch */
+  float* x_f32; void* x_act;                /* [M][d] residual stream and its act-typed copy               */
+  float* qkv;                               /* [M][3d]                                                     */
+  void* ctx;                                /* act [M][d]                                                  */
+  float* y;                                 /* [M][d]                                                      */
+  void* ffn_h;                              /* act [M][F]                                                  */
+  float* logits;                            /* [M][V]                                                      */
+  float* cand_val; int* cand_idx;           /* [M][n_chunk][KT]                                            */
+  float* chunk_max; float* chunk_sum;       /* [M][n_chunk]                                                */
+  int* sent_counter;                        /* [B] zero-initialised                                        */
+} itb_config;
+
+typedef struct itb_decoder itb_decoder;
+
+int         itb_abi_version(void);
+const char* itb_last_error(void);
+int         itb_topk_capacity(int beam);   /* KT: candidate slots per chunk for this beam width */
+
+/* -------- single ops (kernel-level entry points; also used by the parity tests) -------- */
+
+/* out[M][N] = epi(A[M][K] . W[N][K]^T + bias[N]).  Replaces every nn.Linear on the path
+ * (HF BertSelfAttention.query/key/value, BertSelfOutput.dense, BertIntermediate.dense,
+ * BertOutput.dense; reference src/bert_seq2seq.py:9-12 for the vocabulary projection).
+ * dtype = type of A and W; ldo = row stride of `out` in elements. */
+int itb_linear(int dtype, int impl, int epi, const void* A, const void* W, const float* bias, void* out,
+               int M, int N, int K, int ldo, void* stream);
+
+/* x = LayerNorm(word[tok] + pos[step-1] + type[lang]); HF BertEmbeddings (Appendix A.2), for the ONE
+ * new token of each row (reference recomputes the whole prefix: src/seq_gen.py:164-166). */
+int itb_embed_ln(int dtype, const itb_ctl* ctl, const int* tokens, const int* tgt_lang, const float* word,
+                 const float* pos, const float* type, const float* g, const float* b, float eps, float* x_f32,
+                 void* x_act, int M, int beam, int d, int T_max, void* stream);
+
+/* x = LayerNorm(y + x) in place on x_f32, and act copy.  HF BertSelfOutput / BertOutput (A.4, A.6). */
+int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, const float* g, const float* b, float eps,
+               float* x_f32, void* x_act, int M, int d, void* stream);
+
+/* Single-query causal self-attention over the KV cache through the ancestor table; appends the
+ * row's new K,V at position step-1.  HF BertSelfAttention (A.3) on the last position only. */
+int itb_self_attention(int dtype, const itb_ctl* ctl, const float* qkv, void* kv_layer, const unsigned char* anc,
+                       void* ctx, int M, int beam, int d, int H, int T_max, void* stream);
+
+/* Single-query cross-attention over the per-sentence memory K,V with the additive -10000 source mask
+ * (reference src/bert_seq2seq.py:25-38). q has row stride ldq. */
+int itb_cross_attention(int dtype, const itb_ctl* ctl, const float* q, int ldq, const void* cross_kv, int layer,
+                        const unsigned char* src_mask, void* ctx, int M, int beam, int d, int H, int S, int L,
+                        void* stream);
+
+/* Fused log-softmax + finished/over-length row zeroing + score add + length-penalty divide + top-k over
+ * beam*V + forced-PAD rewrites + back-pointer / prefix / size / score / ancestor-table update + termination
+ * bookkeeping.  Replaces reference src/seq_gen.py:134-143 and :194-227. */
+int itb_beam_step(const itb_config* cfg_host, void* stream);
+
+/* Writes slot 0 of every sentence: out_tokens[B][T_max] and out_len[B] (first-EOS cut or max_lens;
+ * reference src/seq_gen.py:229-231 and :6-24).  out_len2[B] = number of tokens produced (unpad_output=False). */
+int itb_finalize(const itb_ctl* ctl, const int* tokens, const int* max_lens, int eos, int* out_tokens, int* out_len,
+                 int* out_len_full, int B, int beam, int T_max, void* stream);
+
+/* Resets ctl and the search state for a new batch (seq_gen.py:109-123). first_tokens: [B]. */
+int itb_init_state(const itb_config* cfg_host, const int* first_tokens, int max_len, void* stream);
+
+/* -------- whole decoder step -------- */
+int itb_decoder_create(const itb_config* cfg_host, itb_decoder** out);
+int itb_decoder_destroy(itb_decoder* dec);
+/* Enqueues one full search step i (embed -> L decoder layers -> vocab projection -> beam step).
+ * Graph-capturable: the step index lives in cfg->ctl. */
+int itb_decoder_step(itb_decoder* dec, void* stream);
+/* One-off per batch: cross K,V of all layers = memory[B*S][d] . Wckv[L*2d][d]^T + b  (HF BertSelfAttention
+ * key/value on encoder_hidden_states; the reference redoes it every step: SURVEY K5). */
+int itb_cross_kv(int dtype, int impl, const void* memory, const void* w_ckv, const float* b_ckv, void* cross_kv,
+                 int rows, int d, int L, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
