@@ -73,6 +73,8 @@ extern "C" {
 
 int itb_abi_version(void) { return ITB_ABI_VERSION; }
 const char* itb_last_error(void) { return g_err; }
+int itb_sizeof_config(void) { return (int)sizeof(itb_config); }
+int itb_sizeof_layer(void) { return (int)sizeof(itb_layer); }
 
 int itb_linear(int dtype, int impl, int epi, const void* A, const void* W, const float* bias, void* out, int M, int N,
                int K, int ldo, void* stream) {

@@ -1,0 +1,206 @@
+"""Host side of the decode path: weight packing, workspace, and the step loop over the C ABI.
+
+Data layout in HBM (all allocated once per engine and reused across batches; kernels never allocate):
+  weights    per decoder layer: Wqkv [3d][d] (query|key|value stacked), Wo, Wcq, Wco [d][d], W1 [F][d], W2 [d][F]
+             in the compute dtype; biases / LayerNorm parameters / embedding tables in fp32;
+             cross K,V projections of ALL layers stacked into one [L*2d][d] matrix (one GEMM per batch).
+  cross_kv   [B][S][L][2][d]      cross-attention K,V, computed once per batch (reference: every step)
+  kv_self    [L][M][T][2][d]      self-attention KV cache, M = B*beam rows; NEVER reordered: the beam kernel
+                                  maintains anc[M][T] (which beam slot physically holds position p)
+  tokens/anc/scores/sizes/fin     ping-pong search state written by the fused beam kernel
+  logits     [M][V4] fp32         the only (M,V)-sized tensor; written by the vocab GEMM, read once
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+_ACT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16}
+
+
+def _lin(mod):
+    return mod.weight.detach(), mod.bias.detach()
+
+
+class PackedDecoder(object):
+    """Device-resident weights of ONE decoder (+ its output layer) in kernel layout.
+
+    Source parameter names are the reference's state-dict keys:
+    decoder.embeddings.*, decoder.decoder.layer.N.{attention,crossattention}.{self.{query,key,value},output.dense,
+    output.LayerNorm}, .intermediate.dense, .output.{dense,LayerNorm}; output_layer[.K].layer.{weight,bias}.
+    """
+
+    def __init__(self, decoder, output_layer, dtype_code, device):
+        act = _ACT[dtype_code]
+        self.dtype_code = dtype_code
+        self._src = []
+
+        def f32(t):
+            self._src.append(t)
+            return t.detach().to(device=device, dtype=torch.float32).contiguous()
+
+        def mat(t):
+            self._src.append(t)
+            return t.detach().to(device=device, dtype=act).contiguous()
+
+        emb = decoder.embeddings
+        self.emb_word, self.emb_pos, self.emb_type = (f32(emb.word_embeddings.weight), f32(emb.position_embeddings.weight),
+                                                      f32(emb.token_type_embeddings.weight))
+        self.emb_ln_g, self.emb_ln_b = f32(emb.LayerNorm.weight), f32(emb.LayerNorm.bias)
+        self.ln_eps = float(emb.LayerNorm.eps)
+        self.n_pos = emb.position_embeddings.weight.shape[0]
+        layers = decoder.decoder.layer
+        self.L = len(layers)
+        self.d = emb.word_embeddings.weight.shape[1]
+        self.H = layers[0].attention.self.num_attention_heads
+        self.F = layers[0].intermediate.dense.weight.shape[0]
+        self.keep = []
+        self.layers = (_lib.Layer * self.L)()
+        ckv_w, ckv_b = [], []
+        for i, ly in enumerate(layers):
+            sa, ca = ly.attention, ly.crossattention
+            for m in (sa.self.query, sa.self.key, sa.self.value, ca.self.key, ca.self.value):
+                self._src.extend([m.weight, m.bias])
+            wqkv = torch.cat([sa.self.query.weight, sa.self.key.weight, sa.self.value.weight], 0).detach().to(device, act).contiguous()
+            bqkv = torch.cat([sa.self.query.bias, sa.self.key.bias, sa.self.value.bias], 0).detach().to(device, torch.float32).contiguous()
+            ckv_w += [ca.self.key.weight.detach(), ca.self.value.weight.detach()]
+            ckv_b += [ca.self.key.bias.detach(), ca.self.value.bias.detach()]
+            t = dict(w_qkv=wqkv, b_qkv=bqkv,
+                     w_o=mat(sa.output.dense.weight), b_o=f32(sa.output.dense.bias),
+                     ln1_g=f32(sa.output.LayerNorm.weight), ln1_b=f32(sa.output.LayerNorm.bias),
+                     w_cq=mat(ca.self.query.weight), b_cq=f32(ca.self.query.bias),
+                     w_co=mat(ca.output.dense.weight), b_co=f32(ca.output.dense.bias),
+                     ln2_g=f32(ca.output.LayerNorm.weight), ln2_b=f32(ca.output.LayerNorm.bias),
+                     w_1=mat(ly.intermediate.dense.weight), b_1=f32(ly.intermediate.dense.bias),
+                     w_2=mat(ly.output.dense.weight), b_2=f32(ly.output.dense.bias),
+                     ln3_g=f32(ly.output.LayerNorm.weight), ln3_b=f32(ly.output.LayerNorm.bias))
+            self.keep.append(t)
+            for k, v in t.items():
+                setattr(self.layers[i], k, v.data_ptr())
+        self.w_ckv = torch.cat(ckv_w, 0).to(device, act).contiguous()          # [L*2d][d]
+        self.b_ckv = torch.cat(ckv_b, 0).to(device, torch.float32).contiguous()
+        self.w_vocab, self.b_vocab = mat(output_layer.layer.weight), f32(output_layer.layer.bias)
+        self.V = self.w_vocab.shape[0]
+        self.versions = tuple(t._version for t in self._src)
+
+    def stale(self):
+        return tuple(t._version for t in self._src) != self.versions
+
+
+class Workspace(object):
+    """Flat device buffers that only ever grow; indexing always uses the CURRENT batch shape."""
+
+    def __init__(self, device):
+        self.device = device
+        self.buf = {}
+
+    def get(self, name, numel, dtype):
+        t = self.buf.get(name)
+        if t is None or t.numel() < numel or t.dtype != dtype:
+            t = torch.empty(max(int(numel), 1), dtype=dtype, device=self.device)
+            self.buf[name] = t
+        return t
+
+
+class DecodeEngine(object):
+    def __init__(self, device, dtype_code, gemm_impl=_lib.GEMM_AUTO, poll_every=16):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("imagetranslate_b200: the decode path runs on CUDA devices only (no CPU fallback)")
+        self.dtype_code = dtype_code
+        self.gemm_impl = gemm_impl
+        self.poll_every = poll_every
+        self.ws = Workspace(self.device)
+        self.lib = _lib.lib()
+        self.last_steps = 0
+        self.launches_per_step = None
+
+    def _config(self, pw, B, beam, S, T_max, pad, eos, alpha):
+        ws, act, M = self.ws, _ACT[self.dtype_code], B * beam
+        V4 = (pw.V + 3) // 4 * 4
+        n_chunk = max(1, min(32, -(-2368 // M), pw.V // 1024 if pw.V >= 1024 else 1))
+        KT = self.lib.itb_topk_capacity(beam)
+        c = _lib.Config()
+        c.dtype, c.gemm_impl = self.dtype_code, self.gemm_impl
+        c.B, c.beam, c.d, c.H, c.F, c.L, c.V, c.S, c.T_max = B, beam, pw.d, pw.H, pw.F, pw.L, pw.V, S, T_max
+        c.pad_id, c.eos_id, c.n_chunk = pad, eos, n_chunk
+        c.len_alpha, c.ln_eps = alpha, pw.ln_eps
+        c.emb_word, c.emb_pos, c.emb_type = pw.emb_word.data_ptr(), pw.emb_pos.data_ptr(), pw.emb_type.data_ptr()
+        c.emb_ln_g, c.emb_ln_b = pw.emb_ln_g.data_ptr(), pw.emb_ln_b.data_ptr()
+        c.layers_host = C.cast(pw.layers, C.c_void_p)
+        c.w_vocab, c.b_vocab = pw.w_vocab.data_ptr(), pw.b_vocab.data_ptr()
+        i32, u8, f32 = torch.int32, torch.uint8, torch.float32
+        t = dict(
+            tgt_lang=ws.get("tgt_lang", B, i32), max_lens=ws.get("max_lens", B, i32),
+            src_mask=ws.get("src_mask", B * S, u8), cross_kv=ws.get("cross_kv", B * S * pw.L * 2 * pw.d, act),
+            ctl=ws.get("ctl", 8, i32), tokens=ws.get("tokens", 2 * M * T_max, i32), anc=ws.get("anc", 2 * M * T_max, u8),
+            scores=ws.get("scores", 2 * M, f32), sizes=ws.get("sizes", 2 * M, f32), fin=ws.get("fin", 2 * M, u8),
+            kv_self=ws.get("kv_self", pw.L * M * T_max * 2 * pw.d, act),
+            x_f32=ws.get("x_f32", M * pw.d, f32), x_act=ws.get("x_act", M * pw.d, act), qkv=ws.get("qkv", M * 3 * pw.d, f32),
+            ctx=ws.get("ctx", M * pw.d, act), y=ws.get("y", M * pw.d, f32), ffn_h=ws.get("ffn_h", M * pw.F, act),
+            logits=ws.get("logits", M * V4, f32), cand_val=ws.get("cand_val", M * n_chunk * KT, f32),
+            cand_idx=ws.get("cand_idx", M * n_chunk * KT, i32), chunk_max=ws.get("chunk_max", M * n_chunk, f32),
+            chunk_sum=ws.get("chunk_sum", M * n_chunk, f32), sent_counter=ws.get("sent_counter", B, i32))
+        for k, v in t.items():
+            setattr(c, k, v.data_ptr())
+        return c, t
+
+    @torch.no_grad()
+    def decode(self, pw, memory, src_mask, first_tokens, tgt_type_ids, max_lens, max_len, beam, pad, eos, alpha, trace=None):
+        """memory (B,S,d) on device; src_mask (B,S) bool or None; first_tokens/tgt_type_ids/max_lens (B,) ints.
+        Returns (tokens (B,T_max) int32 CPU, lengths (B,), full_lengths (B,))."""
+        lib, dev = self.lib, self.device
+        B, S, d = memory.shape
+        if d != pw.d:
+            raise RuntimeError("memory width %d does not match the decoder width %d" % (d, pw.d))
+        T_max = max(int(max_len), 2)
+        cfg, t = self._config(pw, B, beam, S, T_max, pad, eos, alpha)
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        t["tgt_lang"][:B].copy_(tgt_type_ids.to(device=dev, dtype=torch.int32), non_blocking=True)
+        t["max_lens"][:B].copy_(max_lens.to(device=dev, dtype=torch.int32), non_blocking=True)
+        if src_mask is not None:
+            t["src_mask"][:B * S].copy_(src_mask.to(device=dev).reshape(-1).to(torch.uint8), non_blocking=True)
+        else:
+            cfg.src_mask = None
+        first = first_tokens.to(device=dev, dtype=torch.int32).contiguous()
+        mem = memory.to(dtype=_ACT[self.dtype_code]).contiguous()
+        _lib.check(lib.itb_cross_kv(self.dtype_code, self.gemm_impl, _lib.ptr(mem), _lib.ptr(pw.w_ckv), _lib.ptr(pw.b_ckv),
+                                    _lib.ptr(t["cross_kv"]), B * S, pw.d, pw.L, stream), "cross_kv")
+        _lib.check(lib.itb_init_state(C.byref(cfg), _lib.ptr(first), int(max_len), stream), "init_state")
+        dec = C.c_void_p()
+        _lib.check(lib.itb_decoder_create(C.byref(cfg), C.byref(dec)), "decoder_create")
+        try:
+            n_steps = max(int(max_len) - 1, 0)
+            i = 0
+            while i < n_steps:
+                if trace is not None:      # test hook: state BEFORE the step (forces a sync per step)
+                    ctl = t["ctl"][:8].cpu()
+                    if int(ctl[1]) != 0:
+                        break
+                    M, V4 = B * beam, (pw.V + 3) // 4 * 4
+                    cur, step = int(ctl[3]), int(ctl[0])
+                    pre = t["tokens"][:2 * M * T_max].view(2, M, T_max)[cur, :, :step].clone().cpu()
+                _lib.check(lib.itb_decoder_step(dec, stream), "decoder_step")
+                if trace is not None:
+                    M, V4 = B * beam, (pw.V + 3) // 4 * 4
+                    ctl2 = t["ctl"][:8].cpu()
+                    trace.append(dict(step=step, prefixes=pre,
+                                      logits=t["logits"][:M * V4].view(M, V4)[:, :pw.V].clone().cpu(),
+                                      scores=t["scores"][:2 * M].view(2, M)[int(ctl2[3])].clone().cpu(),
+                                      tokens=t["tokens"][:2 * M * T_max].view(2, M, T_max)[int(ctl2[3]), :, :step + 1].clone().cpu()))
+                i += 1
+                if i % self.poll_every == 0 and i < n_steps and int(t["ctl"][1].item()) != 0:   # ctl.done
+                    break
+            out_tok = self.ws.get("out_tok", B * T_max, torch.int32)
+            out_len = self.ws.get("out_len", 2 * B, torch.int32)
+            _lib.check(lib.itb_finalize(_lib.ptr(t["ctl"]), _lib.ptr(t["tokens"]), _lib.ptr(t["max_lens"]), eos,
+                                        _lib.ptr(out_tok), _lib.ptr(out_len), C.c_void_p(out_len.data_ptr() + 4 * B),
+                                        B, beam, T_max, stream), "finalize")
+            tok = out_tok[:B * T_max].view(B, T_max).cpu()
+            lens = out_len[:2 * B].cpu()
+            self.last_steps = int(t["ctl"][2].item())
+        finally:
+            lib.itb_decoder_destroy(dec)
+        self.launches_per_step = 2 + 11 * pw.L
+        return tok, lens[:B], lens[B:]

@@ -84,7 +84,9 @@ typedef struct itb_decoder itb_decoder;
 
 int         itb_abi_version(void);
 const char* itb_last_error(void);
-int         itb_topk_capacity(int beam);   /* KT: candidate slots per chunk for this beam width */
+int         itb_topk_capacity(int beam);
+int         itb_sizeof_config(void);      /* sizeof(itb_config) / sizeof(itb_layer): binding self-check */
+int         itb_sizeof_layer(void);   /* KT: candidate slots per chunk for this beam width */
 
 /* -------- single ops (kernel-level entry points; also used by the parity tests) -------- */
 

@@ -1,0 +1,137 @@
+"""End-to-end parity (-m gpu): the drop-in BeamDecoder (CUDA path, through the C ABI) against
+(1) the fixtures produced by the REAL reference in the build container, (2) the oracle on fresh seeded
+inputs, (3) bf16 tolerance protocol of SURVEY.md §7.2-3 / §8c."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from imagetranslate_b200 import BeamDecoder, _lib
+from oracle import cases, restated as R
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+DEV = "cuda:0"
+
+
+def _decode(model, kw, dtype, unpad=True, gemm_impl=_lib.GEMM_AUTO):
+    kw = dict(kw)
+    beam = kw.pop("beam_width")
+    bd = BeamDecoder(model, beam_width=beam, dtype=dtype, gemm_impl=gemm_impl, **cases.GEN)
+    with torch.no_grad():
+        return bd(unpad_output=unpad, **kw), bd
+
+
+@pytest.mark.parametrize("name", sorted(cases.CASES))
+def test_fp32_matches_reference_fixtures(name):
+    z = np.load(os.path.join(GOLD, name + ".npz"))
+    meta = json.loads(str(z["meta"]))
+    model, kw, c = cases.build(name)
+    assert cases.weights_digest(model) == meta["weights_sha256"]
+    model = model.to(DEV)
+    outs, _ = _decode(model, kw, "fp32")
+    assert [len(o) for o in outs] == z["lengths"].tolist()
+    for r, o in enumerate(outs):
+        assert o.device.type == "cpu" and o.dtype == torch.int64
+        assert o.tolist() == z["tokens"][r, :z["lengths"][r]].tolist()
+    full, _ = _decode(model, kw, "fp32", unpad=False)
+    assert torch.stack(full).tolist() == z["full"].tolist()
+
+
+def _fresh_case(seed, V, B, S, beam, dec, eos_bias=0.0):
+    tp = R.FakeTextProcessor(V)
+    torch.manual_seed(seed)
+    model = R.Seq2SeqModel(tp, lang_dec=False, tie_embed=False, enc_layer=1, dec_layer=dec).eval()
+    with torch.no_grad():
+        model.output_layer[1].layer.bias[4] += eos_bias
+    src, mask, pad_idx = cases.make_text_batch(B, S, V, seed + 7)
+    kw = dict(src_inputs=src, src_mask=mask, src_sizes=pad_idx, src_langs=torch.zeros(B, dtype=torch.long),
+              first_tokens=torch.full((B,), 6), tgt_langs=torch.ones(B, dtype=torch.long), pad_idx=0, beam_width=beam)
+    return model, kw
+
+
+@pytest.mark.parametrize("seed,V,B,S,beam,dec,eos_bias", [(21, 4001, 7, 16, 4, 2, 0.0), (22, 2500, 9, 10, 5, 1, 1.3),
+                                                           (23, 3000, 3, 24, 12, 1, 0.9)])
+def test_fp32_matches_oracle_on_fresh_inputs(seed, V, B, S, beam, dec, eos_bias):
+    model, kw = _fresh_case(seed, V, B, S, beam, dec, eos_bias)
+    want = R.beam_search(model, **cases.GEN, **kw)
+    got, _ = _decode(model.to(DEV), kw, "fp32")
+    assert [g.tolist() for g in got] == [w.tolist() for w in want]
+
+
+def test_list_wrapped_kwargs_and_beam_override():
+    """DataParallel-style list-wrapped tensors (seq_gen.py:57-72) and per-call beam_width (:74-75)."""
+    model, kw = _fresh_case(31, 900, 4, 9, 4, 1)
+    want = R.beam_search(model, **cases.GEN, **dict(kw, beam_width=2))
+    bd = BeamDecoder(model.to(DEV), beam_width=4, dtype="fp32", **cases.GEN)
+    kw.pop("beam_width")
+    wrapped = {k: ([v] if torch.is_tensor(v) else v) for k, v in kw.items()}
+    got = bd(beam_width=2, **wrapped)
+    assert [g.tolist() for g in got] == [w.tolist() for w in want]
+
+
+def _round_weights_to_bf16(model):
+    with torch.no_grad():
+        for p in model.parameters():
+            if p.dim() >= 2:
+                p.copy_(p.to(torch.bfloat16).float())
+
+
+@pytest.mark.parametrize("gemm_impl", [_lib.GEMM_TCGEN05, _lib.GEMM_SIMT], ids=["tcgen05", "simt"])
+def test_bf16_teacher_forced_logprob_error(gemm_impl):
+    """bf16 protocol: per-step log-prob error measured on the PRODUCT's own prefixes (so search divergence cannot
+    hide or inflate it): |log_softmax(cuda logits) - log_softmax(fp32 oracle on the same prefix)| <= 1e-2."""
+    model, kw = _fresh_case(41, 6000, 6, 14, 4, 2)
+    _round_weights_to_bf16(model)
+    kw2 = dict(kw)
+    beam = kw2.pop("beam_width")
+    gpu_model = R.Seq2SeqModel(model.text_processor, lang_dec=False, tie_embed=False, enc_layer=1, dec_layer=2).eval()
+    gpu_model.load_state_dict(model.state_dict())
+    bd = BeamDecoder(gpu_model.to(DEV), beam_width=beam, dtype="bf16", gemm_impl=gemm_impl, **cases.GEN)
+    # drive the engine directly to get the per-step trace
+    src, mask = kw["src_inputs"], kw["src_mask"]
+    with torch.no_grad():
+        memory = gpu_model.encode(src, mask.to(DEV), kw["src_langs"].unsqueeze(-1).expand(-1, src.size(1)))[0]
+    eng = bd._engine(torch.device(DEV), _lib.BF16)
+    pw = bd._weights(gpu_model, 1, _lib.BF16, torch.device(DEV))
+    mlf = lambda s: min(int(1.3 * s + 5), 512)
+    max_len = mlf(src.size(1))
+    max_lens = torch.tensor([mlf(int(x)) for x in kw["src_sizes"]])
+    trace = []
+    eng.decode(pw, memory, mask, kw["first_tokens"], kw["tgt_langs"], max_lens, max_len, beam, 0, 4, 0.8, trace=trace)
+    assert len(trace) == max_len - 1
+    worst, worst_top = 0.0, 0.0
+    with torch.no_grad():
+        mem_cpu = model.encode(src, mask, kw["src_langs"].unsqueeze(-1).expand(-1, src.size(1)))[0]
+        for t in trace[:: max(1, len(trace) // 8)]:
+            pre = t["prefixes"].long()                                  # (M, i)
+            M = pre.size(0)
+            st = model.decoder(encoder_states=mem_cpu.repeat_interleave(beam, 0), input_ids=pre,
+                               encoder_attention_mask=mask.repeat_interleave(beam, 0),
+                               token_type_ids=torch.ones_like(pre))[:, -1]
+            want = torch.log_softmax(model.output_layer[1](st), -1)
+            got = torch.log_softmax(t["logits"].float(), -1)
+            worst = max(worst, float((got - want).abs().max()))
+            top = want.topk(8, -1).indices
+            worst_top = max(worst_top, float((got.gather(1, top) - want.gather(1, top)).abs().max()))
+    print("bf16 teacher-forced log-prob error: max over vocab %.3e, max over top-8 %.3e" % (worst, worst_top))
+    assert worst_top <= 1e-2 and worst <= 2e-2
+
+
+def test_bf16_token_agreement_on_sharpened_weights():
+    """>= 99 % token agreement with the fp32 oracle once the output layer is sharpened x8."""
+    model, kw = _fresh_case(51, 5000, 8, 12, 4, 2)
+    with torch.no_grad():
+        model.output_layer[1].layer.weight.mul_(8.0)
+    _round_weights_to_bf16(model)
+    want = R.beam_search(model, **cases.GEN, **kw)
+    got, _ = _decode(model.to(DEV), kw, "bf16")
+    agree = total = 0
+    for g, w in zip(got, want):
+        n = max(len(g), len(w))
+        total += n
+        agree += sum(1 for a, b in zip(g.tolist(), w.tolist()) if a == b)
+    print("bf16 token agreement %d / %d" % (agree, total))
+    assert agree >= 0.99 * total

@@ -1,0 +1,193 @@
+"""Kernel-level parity (-m gpu): every C-ABI op against a plain torch / oracle restatement of the same math."""
+import ctypes as C
+
+import pytest
+import torch
+
+from imagetranslate_b200 import _lib
+from oracle import restated as R
+
+from gpu_util import ACT, DEV, BeamHarness, linear, make_ctl, rel_err, stream
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(shape, seed, scale=1.0, dtype=torch.float32):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(DEV).to(dtype)
+
+
+# ------------------------------------------------------------------------------------------------ GEMM
+@pytest.mark.parametrize("M,N,K", [(5, 200, 64), (61, 768, 768), (244, 2304, 768), (70, 768, 3072), (130, 1000, 768)])
+@pytest.mark.parametrize("epi", [_lib.EPI_BIAS_F32, _lib.EPI_BIAS_GELU_ACT, _lib.EPI_BIAS_ACT])
+def test_linear_f32_cuda_cores(M, N, K, epi):
+    A, W, b = _rand((M, K), 1), _rand((N, K), 2, 0.05), _rand((N,), 3)
+    ref = A.double() @ W.double().t() + b.double()
+    if epi == _lib.EPI_BIAS_GELU_ACT:
+        ref = torch.nn.functional.gelu(ref)
+    out = linear(_lib.F32, _lib.GEMM_AUTO, epi, A, W, b)
+    assert rel_err(out, ref) < 2e-6
+
+
+@pytest.mark.parametrize("impl", [_lib.GEMM_SIMT, _lib.GEMM_TCGEN05], ids=["simt", "tcgen05"])
+@pytest.mark.parametrize("M,N,K", [(7, 256, 64), (32, 768, 768), (60, 2304, 768), (100, 768, 3072), (244, 3072, 768),
+                                   (300, 1000, 768), (940, 768, 768), (244, 60000, 768), (16, 9216, 768)])
+def test_linear_bf16(impl, M, N, K):
+    A, W, b = _rand((M, K), 4, 1.0, torch.bfloat16), _rand((N, K), 5, 0.05, torch.bfloat16), _rand((N,), 6)
+    ref = A.double() @ W.double().t() + b.double()
+    out = linear(_lib.BF16, impl, _lib.EPI_BIAS_F32, A, W, b)
+    assert torch.isfinite(out).all()
+    assert rel_err(out, ref) < 2e-5          # bf16 products are exact in fp32; only the summation order differs
+    out2 = linear(_lib.BF16, impl, _lib.EPI_BIAS_GELU_ACT, A, W, b)
+    assert rel_err(out2.float(), torch.nn.functional.gelu(ref)) < 6e-3
+    out3 = linear(_lib.BF16, impl, _lib.EPI_BIAS_ACT, A, W, b)
+    assert rel_err(out3.float(), ref) < 6e-3
+
+
+def test_linear_tcgen05_back_to_back_is_deterministic():
+    A, W, b = _rand((244, 768), 7, 1.0, torch.bfloat16), _rand((3072, 768), 8, 0.05, torch.bfloat16), _rand((3072,), 9)
+    o1 = linear(_lib.BF16, _lib.GEMM_TCGEN05, _lib.EPI_BIAS_F32, A, W, b)
+    for _ in range(3):
+        assert torch.equal(o1, linear(_lib.BF16, _lib.GEMM_TCGEN05, _lib.EPI_BIAS_F32, A, W, b))
+
+
+# ------------------------------------------------------------------------------------------------ LN kernels
+@pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16])
+def test_embed_ln_and_add_ln(dtype):
+    M, beam, d, T, V = 12, 4, 768, 9, 50
+    step = 3
+    tokens = torch.randint(0, V, (2, M, T), dtype=torch.int32, device=DEV)
+    lang = torch.tensor([0, 1, 1], dtype=torch.int32, device=DEV)
+    word, pos, typ = _rand((V, d), 1, 0.02), _rand((512, d), 2, 0.02), _rand((2, d), 3, 0.02)
+    g, b = _rand((d,), 4) * 0.1 + 1.0, _rand((d,), 5, 0.1)
+    ctl = make_ctl(step=step, cur=1)
+    xf = torch.zeros(M, d, device=DEV)
+    xa = torch.zeros(M, d, device=DEV, dtype=ACT[dtype])
+    l = _lib.lib()
+    _lib.check(l.itb_embed_ln(dtype, _lib.ptr(ctl), _lib.ptr(tokens), _lib.ptr(lang), _lib.ptr(word), _lib.ptr(pos),
+                              _lib.ptr(typ), _lib.ptr(g), _lib.ptr(b), 1e-12, _lib.ptr(xf), _lib.ptr(xa), M, beam, d, T,
+                              stream()))
+    torch.cuda.synchronize()
+    tok = tokens[1, :, step - 1].long()
+    e = word[tok] + pos[step - 1][None] + typ[lang.long().repeat_interleave(beam)]
+    ref = torch.nn.functional.layer_norm(e, (d,), g, b, 1e-12)
+    assert (xf - ref).abs().max() < 2e-5
+    assert (xa.float() - ref).abs().max() < (2e-5 if dtype == _lib.F32 else 3e-2)
+    y = _rand((M, d), 6)
+    ref2 = torch.nn.functional.layer_norm(y + xf, (d,), g, b, 1e-12)
+    _lib.check(l.itb_add_ln(dtype, _lib.ptr(ctl), _lib.ptr(y), _lib.ptr(g), _lib.ptr(b), 1e-12, _lib.ptr(xf), _lib.ptr(xa),
+                            M, d, stream()))
+    torch.cuda.synchronize()
+    assert (xf - ref2).abs().max() < 2e-5
+
+
+# ------------------------------------------------------------------------------------------------ attention
+@pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16])
+@pytest.mark.parametrize("step", [1, 2, 40])
+def test_self_attention_through_ancestor_table(dtype, step):
+    B, beam, d, H, T = 3, 4, 768, 12, 48
+    M, pc = B * beam, step - 1
+    act = ACT[dtype]
+    qkv = _rand((M, 3 * d), 11)
+    kv = _rand((M, T, 2, d), 12).to(act)
+    g = torch.Generator().manual_seed(13)
+    anc = torch.randint(0, beam, (2, M, T), generator=g).to(torch.uint8).to(DEV)
+    ctl = make_ctl(step=step, cur=1)
+    ctx = torch.zeros(M, d, device=DEV, dtype=act)
+    kv_before = kv.clone()
+    _lib.check(_lib.lib().itb_self_attention(dtype, _lib.ptr(ctl), _lib.ptr(qkv), _lib.ptr(kv), _lib.ptr(anc), _lib.ptr(ctx),
+                                             M, beam, d, H, T, stream()))
+    torch.cuda.synchronize()
+    q, kn, vn = qkv[:, :d], qkv[:, d:2 * d].to(act), qkv[:, 2 * d:].to(act)
+    # append check
+    assert torch.equal(kv[:, pc, 0], kn) and torch.equal(kv[:, pc, 1], vn)
+    other = torch.ones(T, dtype=torch.bool); other[pc] = False
+    assert torch.equal(kv[:, other], kv_before[:, other])
+    rows = torch.arange(M, device=DEV)
+    base = (rows // beam) * beam
+    ref = torch.zeros(M, d, device=DEV, dtype=torch.float64)
+    for r in range(M):
+        phys = base[r] + anc[1, r, :pc].long()
+        K = torch.cat([kv_before[phys, torch.arange(pc), 0], kn[r:r + 1]], 0).double().view(pc + 1, H, 64)
+        Vv = torch.cat([kv_before[phys, torch.arange(pc), 1], vn[r:r + 1]], 0).double().view(pc + 1, H, 64)
+        s = torch.einsum("hd,phd->hp", q[r].double().view(H, 64), K) / 8.0
+        p = torch.softmax(s, -1)
+        ref[r] = torch.einsum("hp,phd->hd", p, Vv).reshape(d)
+    tol = 1e-5 if dtype == _lib.F32 else 2e-2
+    assert (ctx.double() - ref).abs().max() < tol
+
+
+@pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16])
+@pytest.mark.parametrize("masked", [False, True])
+def test_cross_attention_with_additive_mask(dtype, masked):
+    B, beam, d, H, S, L, layer = 3, 4, 768, 12, 21, 2, 1
+    M = B * beam
+    act = ACT[dtype]
+    q = _rand((M, 3 * d), 21)
+    ckv = _rand((B, S, L, 2, d), 22).to(act)
+    mask = torch.ones(B, S, dtype=torch.uint8, device=DEV)
+    if masked:
+        mask[0, 15:] = 0
+        mask[2, 3:] = 0
+    ctx = torch.zeros(M, d, device=DEV, dtype=act)
+    _lib.check(_lib.lib().itb_cross_attention(dtype, None, _lib.ptr(q), 3 * d, _lib.ptr(ckv), layer,
+                                              _lib.ptr(mask) if masked else None, _lib.ptr(ctx), M, beam, d, H, S, L, stream()))
+    torch.cuda.synchronize()
+    K = ckv[:, :, layer, 0].double().view(B, S, H, 64).repeat_interleave(beam, 0)
+    V = ckv[:, :, layer, 1].double().view(B, S, H, 64).repeat_interleave(beam, 0)
+    s = torch.einsum("mhd,mshd->mhs", q[:, :d].double().view(M, H, 64), K) / 8.0
+    s = s + ((1.0 - mask.double()) * -10000.0).repeat_interleave(beam, 0)[:, None, :]
+    ref = torch.einsum("mhs,mshd->mhd", torch.softmax(s, -1), V).reshape(M, d)
+    tol = 1e-5 if dtype == _lib.F32 else 2e-2
+    assert (ctx.double() - ref).abs().max() < tol
+
+
+# ------------------------------------------------------------------------------------------------ fused beam step
+def _oracle_state(B, first_tokens):
+    prefixes = torch.tensor(first_tokens).view(B, 1)
+    return prefixes, torch.zeros(B, 1), None
+
+
+@pytest.mark.parametrize("beam,V,n_chunk", [(4, 2000, 4), (1, 777, 1), (8, 3000, 7), (12, 5003, 3), (3, 60000, 16)])
+def test_beam_step_matches_reference_semantics(beam, V, n_chunk):
+    B, T, eos, pad, alpha = 5, 12, 4, 0, 0.8
+    max_lens = [12, 5, 7, 12, 3]
+    first = [6] * B
+    h = BeamHarness(B, beam, V, T, max_lens, first, max_len=T, pad=pad, eos=eos, alpha=alpha, n_chunk=n_chunk)
+    prefixes = torch.tensor(first).view(B, 1)
+    scores = torch.zeros(B, 1)
+    sizes = torch.zeros(B) if beam > 1 else None
+    mlt = torch.tensor(max_lens)
+    g = torch.Generator().manual_seed(100 + beam)
+    for i in range(1, T):
+        cur = prefixes.view(-1, prefixes.size(-1))
+        all_fin = int(torch.any(cur == eos, 1).sum()) == cur.size(0)
+        assert h.ctl()[1] == (1 if all_fin else 0)
+        if all_fin:
+            break
+        M = B * beam
+        logits = torch.randn(M, V, generator=g) * 2.0
+        if i in (2, 3, 5):                       # make EOS win for some rows so rows finish at different times
+            logits[torch.randperm(M, generator=g)[: M // 3], eos] += 12.0
+        h.step(logits)
+        rows = logits if i > 1 else logits.view(B, beam, V)[:, 0]
+        logp = torch.log_softmax(rows, -1)
+        prefixes, scores, sizes, _ = R.search_step(i, logp, prefixes, scores, sizes, mlt, eos, pad, beam, alpha,
+                                                   topk_fn=R.lowest_index_topk)
+        tok, sc, sz, anc = h.state()
+        assert tok.tolist() == prefixes.tolist(), "prefixes differ at step %d" % i
+        assert torch.allclose(sc, scores, rtol=1e-5, atol=1e-6), "scores differ at step %d" % i
+        if beam > 1:
+            assert sz.tolist() == sizes.tolist()
+    assert h.ctl()[2] >= 3
+
+
+def test_beam_step_is_a_noop_after_termination():
+    h = BeamHarness(2, 4, 1000, 6, [6, 6], [6, 6], max_len=3)
+    h.step(torch.randn(8, 1000))
+    h.step(torch.randn(8, 1000))
+    assert h.ctl()[1] == 1 and h.ctl()[2] == 2          # max_len 3 => exactly 2 steps (seq_gen.py:131)
+    before = h.state()
+    h.step(torch.randn(8, 1000))
+    after = h.state()
+    assert h.ctl()[2] == 2 and all(torch.equal(a, b) for a, b in zip(before, after))
