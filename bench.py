@@ -34,7 +34,7 @@ def parse():
     ap.add_argument("--sentences", type=int, default=4096, help="sentences per rank per step")
     ap.add_argument("--batch", type=int, default=4000)
     ap.add_argument("--capacity", type=int, default=600)
-    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "bf16_f16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sentences", type=int, default=6)
     return ap.parse_args()
@@ -173,7 +173,7 @@ def run_b200(args, rank, world, local_rank):
     torch.manual_seed(0)
     model = MassSeq2Seq(SyntheticTextProcessor(VOCAB), lang_dec=False, tie_embed=False, enc_layer=ENC, dec_layer=DEC).eval()
     model = model.to(dev)
-    if args.dtype == "bf16":
+    if args.dtype != "fp32":
         model = model.to(torch.bfloat16)
     gen = BeamDecoder(model, beam_width=BEAM, dtype=args.dtype, **GEN)
     batches = build_batches(args.sentences, 1234 + rank, args.batch, args.capacity)
@@ -244,7 +244,7 @@ def run_b200(args, rank, world, local_rank):
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
-        if args.dtype == "bf16":
+        if args.dtype != "fp32":
             rf = time_kernel_rooflines(gen, model, peaks)
             line["roofline"] = rf["vocab_gemm"]
             line["roofline"]["peak_source"] = "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650 GB/s"

@@ -52,6 +52,28 @@ template <> struct RowLoad<__nv_bfloat16> {
 };
 
 // Shared tail: softmax over sc[0..n) (+ optional extra current-position score) and P.V accumulation.
+template <> struct RowLoad<__half> {
+    static __device__ __forceinline__ float dot(const __half* k, const float* q) {
+        const uint4* k4 = reinterpret_cast<const uint4*>(k);
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < DH / 8; ++j) {
+            uint4 u = k4[j];
+            const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                float2 f = __half22float2(h[e]);
+                acc = fmaf(f.x, q[8 * j + 2 * e + 0], acc);
+                acc = fmaf(f.y, q[8 * j + 2 * e + 1], acc);
+            }
+        }
+        return acc;
+    }
+    static __device__ __forceinline__ float2 pair(const __half* v, int lane) {
+        return __half22float2(reinterpret_cast<const __half2*>(v)[lane]);
+    }
+};
+
 template <typename T, typename VPtr>
 __device__ __forceinline__ void softmax_pv(float* sc, int n, bool has_cur, float s_cur, float2 v_cur, VPtr vptr,
                                            int lane, float2& out) {
@@ -193,6 +215,7 @@ int itb_self_attention(int dtype, const itb_ctl* ctl, const float* qkv, void* kv
     ITB_REQUIRE(T_max <= 2048, "self_attention: T_max too large for the shared-memory score buffer");
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
     if (dtype == ITB_BF16) return launch_self<__nv_bfloat16>(c, qkv, kv_layer, anc, ctx, M, beam, d, H, T_max, (cudaStream_t)stream);
+    if (dtype == ITB_BF16_F16) return launch_self<__half>(c, qkv, kv_layer, anc, ctx, M, beam, d, H, T_max, (cudaStream_t)stream);
     return launch_self<float>(c, qkv, kv_layer, anc, ctx, M, beam, d, H, T_max, (cudaStream_t)stream);
 }
 
@@ -203,6 +226,7 @@ int itb_cross_attention(int dtype, const itb_ctl* ctl, const float* q, int ldq, 
     ITB_REQUIRE(S <= 2048, "cross_attention: S too large for the shared-memory score buffer");
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
     if (dtype == ITB_BF16) return launch_cross<__nv_bfloat16>(c, q, ldq, cross_kv, layer, src_mask, ctx, M, beam, d, H, S, L, (cudaStream_t)stream);
+    if (dtype == ITB_BF16_F16) return launch_cross<__half>(c, q, ldq, cross_kv, layer, src_mask, ctx, M, beam, d, H, S, L, (cudaStream_t)stream);
     return launch_cross<float>(c, q, ldq, cross_kv, layer, src_mask, ctx, M, beam, d, H, S, L, (cudaStream_t)stream);
 }
 

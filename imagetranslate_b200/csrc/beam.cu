@@ -135,6 +135,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
         if (w == 0) {
             const size_t o = ((size_t)r * a.n_chunk + c) * KT;
             warp_select(s_val, s_idx, 8 * KT, K, a.cand_val + o, a.cand_idx + o, lane);
+            if (lane >= K && lane < KT) { a.cand_val[o + lane] = -INFINITY; a.cand_idx[o + lane] = -1; }   // unused slots
             if (lane == 0) {
                 float mm = -INFINITY, ss = 0.f;
                 for (int j = 0; j < 8; ++j) mm = fmaxf(mm, s_m[j]);

@@ -24,9 +24,18 @@ template <> struct Ld8<__nv_bfloat16> {
     }
 };
 
-template <typename T, int EPI>
+template <> struct Ld8<__half> {
+    static __device__ __forceinline__ void ld(const __half* p, float* o) {
+        uint4 u = *reinterpret_cast<const uint4*>(p);
+        const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { float2 f = __half22float2(h[e]); o[2 * e] = f.x; o[2 * e + 1] = f.y; }
+    }
+};
+
+template <typename T, typename TW, int EPI>
 __global__ void __launch_bounds__(256) gemm_simt_kernel(const ItbCtl* __restrict__ ctl, const T* __restrict__ A,
-                                                        const T* __restrict__ W, const float* __restrict__ bias,
+                                                        const TW* __restrict__ W, const float* __restrict__ bias,
                                                         void* __restrict__ out, int M, int N, int K, int ldo) {
     __shared__ float As[BK][BM + 4];
     __shared__ float Ws[BK][BN + 4];
@@ -47,7 +56,7 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const ItbCtl* __restrict
 #pragma unroll
             for (int e = 0; e < 8; ++e) av[e] = 0.f;
         }
-        if (n0 + lr < N) Ld8<T>::ld(W + (size_t)(n0 + lr) * K + k0 + lk, wv);
+        if (n0 + lr < N) Ld8<TW>::ld(W + (size_t)(n0 + lr) * K + k0 + lk, wv);
         else {
 #pragma unroll
             for (int e = 0; e < 8; ++e) wv[e] = 0.f;
@@ -85,14 +94,14 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const ItbCtl* __restrict
     }
 }
 
-template <typename T>
+template <typename T, typename TW>
 static int launch_simt(int epi, const ItbCtl* ctl, const void* A, const void* W, const float* bias, void* out, int M,
                        int N, int K, int ldo, cudaStream_t s) {
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
-    const T* a = (const T*)A; const T* w = (const T*)W;
-    if (epi == ITB_EPI_BIAS_F32) gemm_simt_kernel<T, ITB_EPI_BIAS_F32><<<grid, 256, 0, s>>>(ctl, a, w, bias, out, M, N, K, ldo);
-    else if (epi == ITB_EPI_BIAS_GELU_ACT) gemm_simt_kernel<T, ITB_EPI_BIAS_GELU_ACT><<<grid, 256, 0, s>>>(ctl, a, w, bias, out, M, N, K, ldo);
-    else gemm_simt_kernel<T, ITB_EPI_BIAS_ACT><<<grid, 256, 0, s>>>(ctl, a, w, bias, out, M, N, K, ldo);
+    const T* a = (const T*)A; const TW* w = (const TW*)W;
+    if (epi == ITB_EPI_BIAS_F32) gemm_simt_kernel<T, TW, ITB_EPI_BIAS_F32><<<grid, 256, 0, s>>>(ctl, a, w, bias, out, M, N, K, ldo);
+    else if (epi == ITB_EPI_BIAS_GELU_ACT) gemm_simt_kernel<T, TW, ITB_EPI_BIAS_GELU_ACT><<<grid, 256, 0, s>>>(ctl, a, w, bias, out, M, N, K, ldo);
+    else gemm_simt_kernel<T, TW, ITB_EPI_BIAS_ACT><<<grid, 256, 0, s>>>(ctl, a, w, bias, out, M, N, K, ldo);
     return itb_check_launch("gemm_simt");
 }
 
@@ -101,6 +110,7 @@ int itb_gemm_simt(int dtype, int epi, const void* ctl, const void* A, const void
     ITB_REQUIRE(K % BK == 0, "linear: K must be a multiple of 32");
     ITB_REQUIRE(M > 0 && N > 0, "linear: empty problem");
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
-    if (dtype == ITB_BF16) return launch_simt<__nv_bfloat16>(epi, c, A, W, bias, out, M, N, K, ldo, s);
-    return launch_simt<float>(epi, c, A, W, bias, out, M, N, K, ldo, s);
+    if (dtype == ITB_BF16) return launch_simt<__nv_bfloat16, __nv_bfloat16>(epi, c, A, W, bias, out, M, N, K, ldo, s);
+    if (dtype == ITB_BF16_F16) return launch_simt<__half, __nv_bfloat16>(epi, c, A, W, bias, out, M, N, K, ldo, s);
+    return launch_simt<float, float>(epi, c, A, W, bias, out, M, N, K, ldo, s);
 }

@@ -100,7 +100,7 @@ template <int MT, int EPI>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
                const ItbCtl* __restrict__ ctl, const float* __restrict__ bias, void* __restrict__ out, int M, int N,
-               int K, int ldo) {
+               int K, int ldo, int act_f16) {
     using Cfg = TcCfg<MT>;
     extern __shared__ uint8_t smem_raw[];
     if (ctl != nullptr && ctl->done) return;           // uniform early-out, before any barrier / TMEM allocation
@@ -153,8 +153,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            // instruction descriptor: D=f32 (bit 4), A=B=bf16 (bits 7, 10), both K-major, N=MT (>>3 @17), M=128 (>>4 @24)
-            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(MT >> 3) << 17) | ((uint32_t)(TC_BN >> 4) << 24);
+            // instruction descriptor: D=f32 (bit 4); UMMA-A (weights) = bf16 (1 @7); UMMA-B (activations) = bf16 (1 @10) or
+            // f16 (0 @10); both K-major; N=MT (>>3 @17); M=128 (>>4 @24)
+            const uint32_t idesc = (1u << 4) | (1u << 7) | ((act_f16 ? 0u : 1u) << 10) | ((uint32_t)(MT >> 3) << 17) | ((uint32_t)(TC_BN >> 4) << 24);
             uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
                 mbar_wait(&tempty[as], aphase ^ 1);
@@ -198,7 +199,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
                             if (EPI == ITB_EPI_BIAS_F32) reinterpret_cast<float*>(out)[(size_t)m * ldo + n] = x;
                             else {
                                 if (EPI == ITB_EPI_BIAS_GELU_ACT) x = gelu_erf(x);
-                                reinterpret_cast<__nv_bfloat16*>(out)[(size_t)m * ldo + n] = __float2bfloat16_rn(x);
+                                if (act_f16) reinterpret_cast<__half*>(out)[(size_t)m * ldo + n] = __float2half_rn(x);
+                                else reinterpret_cast<__nv_bfloat16*>(out)[(size_t)m * ldo + n] = __float2bfloat16_rn(x);
                             }
                         }
                     }
@@ -236,14 +238,14 @@ static PFN_encodeTiled get_encode() {
 }
 
 // 2-D bf16 row-major [rows][K] tensor, box = [box_rows][64], 128-byte swizzle, OOB rows read as zero.
-int itb_make_tmap_bf16(CUtensorMap* map, const void* base, int rows, int K, int box_rows) {
+int itb_make_tmap_16b(CUtensorMap* map, const void* base, int rows, int K, int box_rows, int is_f16) {
     PFN_encodeTiled enc = get_encode();
     if (enc == nullptr) { itb_set_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)"); return -3; }
     cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
     cuuint64_t gstr[1] = {(cuuint64_t)K * 2};
     cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+    CUresult r = enc(map, is_f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { itb_set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%d K=%d box=%d)", (int)r, rows, K, box_rows); return -3; }
@@ -265,7 +267,7 @@ static int num_sms() {
 
 template <int MT, int EPI>
 static int launch_tc(const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCtl* ctl, const float* bias, void* out,
-                     int M, int N, int K, int ldo, cudaStream_t s) {
+                     int M, int N, int K, int ldo, int act_f16, cudaStream_t s) {
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<MT>::kSmemBytes);
@@ -274,27 +276,27 @@ static int launch_tc(const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCt
     }
     const int total = ((N + TC_BN - 1) / TC_BN) * ((M + MT - 1) / MT);
     const int grid = total < num_sms() ? total : num_sms();
-    gemm_tc_kernel<MT, EPI><<<grid, TC_THREADS, TcCfg<MT>::kSmemBytes, s>>>(tmW, tmA, ctl, bias, out, M, N, K, ldo);
+    gemm_tc_kernel<MT, EPI><<<grid, TC_THREADS, TcCfg<MT>::kSmemBytes, s>>>(tmW, tmA, ctl, bias, out, M, N, K, ldo, act_f16);
     return itb_check_launch("gemm_tc");
 }
 
 template <int MT>
 static int launch_tc_epi(int epi, const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCtl* ctl, const float* bias,
-                         void* out, int M, int N, int K, int ldo, cudaStream_t s) {
-    if (epi == ITB_EPI_BIAS_F32) return launch_tc<MT, ITB_EPI_BIAS_F32>(tmW, tmA, ctl, bias, out, M, N, K, ldo, s);
-    if (epi == ITB_EPI_BIAS_GELU_ACT) return launch_tc<MT, ITB_EPI_BIAS_GELU_ACT>(tmW, tmA, ctl, bias, out, M, N, K, ldo, s);
-    return launch_tc<MT, ITB_EPI_BIAS_ACT>(tmW, tmA, ctl, bias, out, M, N, K, ldo, s);
+                         void* out, int M, int N, int K, int ldo, int act_f16, cudaStream_t s) {
+    if (epi == ITB_EPI_BIAS_F32) return launch_tc<MT, ITB_EPI_BIAS_F32>(tmW, tmA, ctl, bias, out, M, N, K, ldo, act_f16, s);
+    if (epi == ITB_EPI_BIAS_GELU_ACT) return launch_tc<MT, ITB_EPI_BIAS_GELU_ACT>(tmW, tmA, ctl, bias, out, M, N, K, ldo, act_f16, s);
+    return launch_tc<MT, ITB_EPI_BIAS_ACT>(tmW, tmA, ctl, bias, out, M, N, K, ldo, act_f16, s);
 }
 
 // tmW: [N][K] box 128 rows; tmA: [M][K] box itb_tc_pick_mt(M) rows.
 int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const void* ctl, const float* bias, void* out,
-                int M, int N, int K, int ldo, cudaStream_t s) {
+                int M, int N, int K, int ldo, int act_f16, cudaStream_t s) {
     ITB_REQUIRE(K % TC_BK == 0 && K >= TC_BK, "linear(tcgen05): K must be a multiple of 64");
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
     switch (itb_tc_pick_mt(M)) {
-        case 32: return launch_tc_epi<32>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, s);
-        case 64: return launch_tc_epi<64>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, s);
-        case 128: return launch_tc_epi<128>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, s);
-        default: return launch_tc_epi<256>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, s);
+        case 32: return launch_tc_epi<32>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, s);
+        case 64: return launch_tc_epi<64>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, s);
+        case 128: return launch_tc_epi<128>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, s);
+        default: return launch_tc_epi<256>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, s);
     }
 }

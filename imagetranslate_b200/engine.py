@@ -16,7 +16,8 @@ import torch
 
 from . import _lib
 
-_ACT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16}
+_ACT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.BF16_F16: torch.float16}      # activations / KV cache
+_WT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.BF16_F16: torch.bfloat16}      # linear weights
 
 
 def _lin(mod):
@@ -32,7 +33,7 @@ class PackedDecoder(object):
     """
 
     def __init__(self, decoder, output_layer, dtype_code, device):
-        act = _ACT[dtype_code]
+        act = _WT[dtype_code]       # weight dtype of every linear
         self.dtype_code = dtype_code
         self._src = []
 

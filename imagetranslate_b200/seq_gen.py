@@ -53,9 +53,11 @@ class BeamDecoder(nn.Module):
     def _dtype_code(self, weight):
         if self.compute_dtype in ("fp32", "float32", "f32"):
             return _lib.F32
-        if self.compute_dtype in ("bf16", "bfloat16", "fp16", "half"):
+        if self.compute_dtype in ("bf16", "bfloat16"):
             return _lib.BF16
-        return _lib.F32 if weight.dtype == torch.float32 else _lib.BF16
+        if self.compute_dtype in ("bf16_f16", "mixed", "fp16", "half"):
+            return _lib.BF16_F16            # bf16 weights, fp16 activations / KV cache (8x finer activation rounding)
+        return _lib.F32 if weight.dtype == torch.float32 else _lib.BF16_F16
 
     def _engine(self, device, code):
         key = (str(device), code)

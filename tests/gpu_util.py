@@ -6,7 +6,7 @@ import torch
 from imagetranslate_b200 import _lib
 
 DEV = "cuda:0"
-ACT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16}
+ACT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.BF16_F16: torch.float16}
 
 
 def stream():
@@ -43,7 +43,10 @@ class BeamHarness(object):
         self.M, self.V4 = M, (V + 3) // 4 * 4
         KT = l.itb_topk_capacity(beam)
         i32, u8, f32 = torch.int32, torch.uint8, torch.float32
-        z = lambda n, dt: torch.zeros(n, dtype=dt, device=DEV)
+        def z(n, dt):     # poisoned, not zero: kernels must never rely on fresh allocations
+            if dt == torch.float32:
+                return torch.full((n,), 3.0e38, dtype=dt, device=DEV)
+            return torch.full((n,), 77, dtype=dt, device=DEV)
         self.t = dict(ctl=z(8, i32), tokens=z(2 * M * T_max, i32), anc=z(2 * M * T_max, u8), scores=z(2 * M, f32),
                       sizes=z(2 * M, f32), fin=z(2 * M, u8), logits=z(M * self.V4, f32), cand_val=z(M * n_chunk * KT, f32),
                       cand_idx=z(M * n_chunk * KT, i32), chunk_max=z(M * n_chunk, f32), chunk_sum=z(M * n_chunk, f32),

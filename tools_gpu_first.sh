@@ -9,8 +9,13 @@ run k_beam    $PT tests/test_gpu_kernels.py -k "beam_step"
 run k_simt16  $PT tests/test_gpu_kernels.py -k "linear_bf16 and simt"
 run k_tc      $PT tests/test_gpu_kernels.py -k "tcgen05"
 run d_fp32    $PT tests/test_gpu_decode.py -k "fp32 or list_wrapped"
-run d_bf16s   $PT tests/test_gpu_decode.py -s -k "teacher_forced and simt"
-run d_bf16t   $PT tests/test_gpu_decode.py -s -k "teacher_forced and tcgen05 or sharpened"
+run d_16s     $PT tests/test_gpu_decode.py -s -k "teacher_forced and simt"
+run d_16t     $PT tests/test_gpu_decode.py -s -k "teacher_forced and tcgen05"
+run d_16x     $PT tests/test_gpu_decode.py -s -k "six_layer or free_running"
 run smoke     python -c "import __graft_entry__ as g; g.smoke()"
 run bench     python bench.py --sentences 512 --steps 1 --warmup 1 --cpu-sentences 2
+run bench16   python bench.py --sentences 512 --steps 1 --warmup 1 --no-cpu-baseline --dtype bf16_f16
 cat gpurun_out/summary.txt
+CMD="python bench.py --sentences 64 --steps 1 --warmup 1 --no-cpu-baseline"
+timeout 300 $CMD > gpurun_out/plain.log 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 3000 -c 700 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu.log 2>&1
+echo "ncu launches exit=$?" | tee -a gpurun_out/summary.txt
