@@ -34,7 +34,7 @@ def parse():
     ap.add_argument("--sentences", type=int, default=4096, help="sentences per rank per step")
     ap.add_argument("--batch", type=int, default=4000)
     ap.add_argument("--capacity", type=int, default=600)
-    ap.add_argument("--dtype", default="bf16", choices=["bf16", "bf16_f16", "fp32"])
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sentences", type=int, default=6)
     return ap.parse_args()

@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libitb.so")
 
-F32, BF16, BF16_F16 = 0, 1, 2      # (weights, activations): (f32,f32) / (bf16,bf16) / (bf16,fp16); include/itb.h
+F32, BF16, F16 = 0, 1, 2      # (weights, activations): (f32,f32) / (bf16,bf16) / (fp16,fp16); include/itb.h
 GEMM_AUTO, GEMM_SIMT, GEMM_TCGEN05 = 0, 1, 2
 EPI_BIAS_F32, EPI_BIAS_GELU_ACT, EPI_BIAS_ACT = 0, 1, 2
 ABI_VERSION = 1

@@ -46,12 +46,12 @@ struct Linear {
     int prepare(int dtype, int impl) {
         tc = use_tc(dtype, impl);
         if (!tc) return 0;
-        int r = itb_make_tmap_16b(&tmW, W, N, K, 128, 0);
+        int r = itb_make_tmap_16b(&tmW, W, N, K, 128, dtype == ITB_F16 ? 1 : 0);
         if (r != 0) return r;
-        return itb_make_tmap_16b(&tmA, A, M, K, itb_tc_pick_mt(M), dtype == ITB_BF16_F16 ? 1 : 0);
+        return itb_make_tmap_16b(&tmA, A, M, K, itb_tc_pick_mt(M), dtype == ITB_F16 ? 1 : 0);
     }
     int run(int dtype, const void* ctl, cudaStream_t s) const {
-        if (tc) return itb_gemm_tc(epi, &tmW, &tmA, ctl, bias, out, M, N, K, ldo, dtype == ITB_BF16_F16 ? 1 : 0, s);
+        if (tc) return itb_gemm_tc(epi, &tmW, &tmA, ctl, bias, out, M, N, K, ldo, dtype == ITB_F16 ? 1 : 0, s);
         return itb_gemm_simt(dtype, epi, ctl, A, W, bias, out, M, N, K, ldo, s);
     }
 };
@@ -78,7 +78,7 @@ int itb_sizeof_layer(void) { return (int)sizeof(itb_layer); }
 
 int itb_linear(int dtype, int impl, int epi, const void* A, const void* W, const float* bias, void* out, int M, int N,
                int K, int ldo, void* stream) {
-    ITB_REQUIRE(dtype == ITB_F32 || dtype == ITB_BF16 || dtype == ITB_BF16_F16, "linear: unknown dtype");
+    ITB_REQUIRE(dtype == ITB_F32 || dtype == ITB_BF16 || dtype == ITB_F16, "linear: unknown dtype");
     ITB_REQUIRE(!(impl == ITB_GEMM_TCGEN05 && dtype == ITB_F32), "linear: the tcgen05 path needs 16-bit operands");
     Linear l = make_linear(A, W, bias, out, M, N, K, ldo, epi);
     int r = l.prepare(dtype, impl);
@@ -93,7 +93,7 @@ int itb_cross_kv(int dtype, int impl, const void* memory, const void* w_ckv, con
 
 int itb_decoder_create(const itb_config* c, itb_decoder** out) {
     ITB_REQUIRE(c != nullptr && out != nullptr, "decoder_create: null argument");
-    ITB_REQUIRE(c->dtype == ITB_F32 || c->dtype == ITB_BF16 || c->dtype == ITB_BF16_F16, "decoder_create: unknown dtype");
+    ITB_REQUIRE(c->dtype == ITB_F32 || c->dtype == ITB_BF16 || c->dtype == ITB_F16, "decoder_create: unknown dtype");
     ITB_REQUIRE(c->d == c->H * 64, "decoder_create: only head_dim 64 is supported (hidden = 64 * heads)");
     ITB_REQUIRE(c->d % 64 == 0 && c->F % 64 == 0, "decoder_create: hidden and FFN sizes must be multiples of 64");
     ITB_REQUIRE(c->beam >= 1 && c->beam <= 16, "decoder_create: beam width must be in [1,16]");

@@ -215,7 +215,7 @@ int itb_self_attention(int dtype, const itb_ctl* ctl, const float* qkv, void* kv
     ITB_REQUIRE(T_max <= 2048, "self_attention: T_max too large for the shared-memory score buffer");
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
     if (dtype == ITB_BF16) return launch_self<__nv_bfloat16>(c, qkv, kv_layer, anc, ctx, M, beam, d, H, T_max, (cudaStream_t)stream);
-    if (dtype == ITB_BF16_F16) return launch_self<__half>(c, qkv, kv_layer, anc, ctx, M, beam, d, H, T_max, (cudaStream_t)stream);
+    if (dtype == ITB_F16) return launch_self<__half>(c, qkv, kv_layer, anc, ctx, M, beam, d, H, T_max, (cudaStream_t)stream);
     return launch_self<float>(c, qkv, kv_layer, anc, ctx, M, beam, d, H, T_max, (cudaStream_t)stream);
 }
 
@@ -226,7 +226,7 @@ int itb_cross_attention(int dtype, const itb_ctl* ctl, const float* q, int ldq, 
     ITB_REQUIRE(S <= 2048, "cross_attention: S too large for the shared-memory score buffer");
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
     if (dtype == ITB_BF16) return launch_cross<__nv_bfloat16>(c, q, ldq, cross_kv, layer, src_mask, ctx, M, beam, d, H, S, L, (cudaStream_t)stream);
-    if (dtype == ITB_BF16_F16) return launch_cross<__half>(c, q, ldq, cross_kv, layer, src_mask, ctx, M, beam, d, H, S, L, (cudaStream_t)stream);
+    if (dtype == ITB_F16) return launch_cross<__half>(c, q, ldq, cross_kv, layer, src_mask, ctx, M, beam, d, H, S, L, (cudaStream_t)stream);
     return launch_cross<float>(c, q, ldq, cross_kv, layer, src_mask, ctx, M, beam, d, H, S, L, (cudaStream_t)stream);
 }
 

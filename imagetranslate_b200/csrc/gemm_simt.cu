@@ -111,6 +111,6 @@ int itb_gemm_simt(int dtype, int epi, const void* ctl, const void* A, const void
     ITB_REQUIRE(M > 0 && N > 0, "linear: empty problem");
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
     if (dtype == ITB_BF16) return launch_simt<__nv_bfloat16, __nv_bfloat16>(epi, c, A, W, bias, out, M, N, K, ldo, s);
-    if (dtype == ITB_BF16_F16) return launch_simt<__half, __nv_bfloat16>(epi, c, A, W, bias, out, M, N, K, ldo, s);
+    if (dtype == ITB_F16) return launch_simt<__half, __half>(epi, c, A, W, bias, out, M, N, K, ldo, s);
     return launch_simt<float, float>(epi, c, A, W, bias, out, M, N, K, ldo, s);
 }

@@ -153,9 +153,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            // instruction descriptor: D=f32 (bit 4); UMMA-A (weights) = bf16 (1 @7); UMMA-B (activations) = bf16 (1 @10) or
-            // f16 (0 @10); both K-major; N=MT (>>3 @17); M=128 (>>4 @24)
-            const uint32_t idesc = (1u << 4) | (1u << 7) | ((act_f16 ? 0u : 1u) << 10) | ((uint32_t)(MT >> 3) << 17) | ((uint32_t)(TC_BN >> 4) << 24);
+            // instruction descriptor: D=f32 (bit 4); UMMA-A (weights) @7 and UMMA-B (activations) @10: bf16 = 1, f16 = 0 -- the two
+            // formats must be EQUAL (a mixed bf16 x f16 descriptor raises an illegal-instruction fault on B200); both K-major; N=MT (>>3 @17); M=128 (>>4 @24)
+            const uint32_t idesc = (1u << 4) | ((act_f16 ? 0u : 1u) << 7) | ((act_f16 ? 0u : 1u) << 10) | ((uint32_t)(MT >> 3) << 17) | ((uint32_t)(TC_BN >> 4) << 24);
             uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
                 mbar_wait(&tempty[as], aphase ^ 1);

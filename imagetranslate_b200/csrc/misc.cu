@@ -142,7 +142,7 @@ int itb_embed_ln(int dtype, const itb_ctl* ctl, const int* tokens, const int* tg
     if (dtype == ITB_BF16)
         embed_ln_kernel<__nv_bfloat16><<<M, 256, smem, s>>>(c, tokens, tgt_lang, word, pos, type, g, b, eps, x_f32,
                                                             (__nv_bfloat16*)x_act, M, beam, d, T_max);
-    else if (dtype == ITB_BF16_F16)
+    else if (dtype == ITB_F16)
         embed_ln_kernel<__half><<<M, 256, smem, s>>>(c, tokens, tgt_lang, word, pos, type, g, b, eps, x_f32,
                                                      (__half*)x_act, M, beam, d, T_max);
     else
@@ -159,7 +159,7 @@ int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, const float* g, co
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
     if (dtype == ITB_BF16)
         add_ln_kernel<__nv_bfloat16><<<M, 256, smem, s>>>(c, y, g, b, eps, x_f32, (__nv_bfloat16*)x_act, M, d);
-    else if (dtype == ITB_BF16_F16)
+    else if (dtype == ITB_F16)
         add_ln_kernel<__half><<<M, 256, smem, s>>>(c, y, g, b, eps, x_f32, (__half*)x_act, M, d);
     else
         add_ln_kernel<float><<<M, 256, smem, s>>>(c, y, g, b, eps, x_f32, (float*)x_act, M, d);

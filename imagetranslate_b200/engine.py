@@ -16,8 +16,8 @@ import torch
 
 from . import _lib
 
-_ACT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.BF16_F16: torch.float16}      # activations / KV cache
-_WT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.BF16_F16: torch.bfloat16}      # linear weights
+_ACT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.F16: torch.float16}      # activations / KV cache
+_WT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.F16: torch.float16}      # linear weights
 
 
 def _lin(mod):

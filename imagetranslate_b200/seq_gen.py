@@ -55,9 +55,9 @@ class BeamDecoder(nn.Module):
             return _lib.F32
         if self.compute_dtype in ("bf16", "bfloat16"):
             return _lib.BF16
-        if self.compute_dtype in ("bf16_f16", "mixed", "fp16", "half"):
-            return _lib.BF16_F16            # bf16 weights, fp16 activations / KV cache (8x finer activation rounding)
-        return _lib.F32 if weight.dtype == torch.float32 else _lib.BF16_F16
+        if self.compute_dtype in ("fp16", "float16", "half"):
+            return _lib.F16            # fp16 weights, activations and KV cache (the reference's --fp16 / apex O2 arithmetic)
+        return _lib.F32 if weight.dtype == torch.float32 else _lib.F16
 
     def _engine(self, device, code):
         key = (str(device), code)

@@ -11,7 +11,7 @@
  * as void*; functions only ENQUEUE work (no sync, no allocation of device memory)
  * and return 0 on success or a negative code, with text from itb_last_error().
  * Matrices are row-major; "act" means the compute dtype of the decoder
- * (ITB_F32: float, ITB_BF16: __nv_bfloat16, ITB_BF16_F16: __half); linear weights are [out][in] exactly
+ * (ITB_F32: float, ITB_BF16: __nv_bfloat16, ITB_F16: __half); linear weights are [out][in] exactly
  * as torch.nn.Linear stores them (HF BertSelfAttention.query.weight etc.).
  */
 #ifndef ITB_H_
@@ -26,7 +26,7 @@ extern "C" {
  * logits and beam scores are always fp32. */
 enum { ITB_F32 = 0,        /* float weights,  float activations   (parity mode, CUDA cores)                 */
        ITB_BF16 = 1,       /* bf16 weights,   bf16 activations    (tcgen05 kind::f16)                        */
-       ITB_BF16_F16 = 2 }; /* bf16 weights,   fp16 activations    (tcgen05 kind::f16, mixed operand formats) */
+       ITB_F16 = 2 };      /* fp16 weights,   fp16 activations    (tcgen05 kind::f16; the reference's --fp16 / apex O2) */
 enum { ITB_GEMM_AUTO = 0, ITB_GEMM_SIMT = 1, ITB_GEMM_TCGEN05 = 2 };
 /* GEMM epilogues */
 enum { ITB_EPI_BIAS_F32 = 0,      /* out f32  = acc + bias                                  */

@@ -6,7 +6,7 @@ import torch
 from imagetranslate_b200 import _lib
 
 DEV = "cuda:0"
-ACT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.BF16_F16: torch.float16}
+ACT = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.F16: torch.float16}
 
 
 def stream():

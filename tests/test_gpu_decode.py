@@ -85,7 +85,7 @@ def _round_weights_to_bf16(model):
                 p.copy_(p.to(torch.bfloat16).float())
 
 
-MODES = {"bf16": _lib.BF16, "bf16_f16": _lib.BF16_F16}
+MODES = {"bf16": _lib.BF16, "fp16": _lib.F16}
 
 
 def _teacher_forced(mode, gemm_impl, dec_layers, seed=41, V=6000, B=6, S=14, beam=4):
@@ -130,27 +130,27 @@ def _teacher_forced(mode, gemm_impl, dec_layers, seed=41, V=6000, B=6, S=14, bea
 
 
 @pytest.mark.parametrize("gemm_impl", [_lib.GEMM_TCGEN05, _lib.GEMM_SIMT], ids=["tcgen05", "simt"])
-@pytest.mark.parametrize("mode", ["bf16", "bf16_f16"])
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
 def test_16bit_teacher_forced_logprob_error(mode, gemm_impl):
     """north_star tolerance: per-step log-prob within 1e-2 abs of the fp32 reference (bf16 weights on both sides)."""
     worst, worst_top, agree, total = _teacher_forced(mode, gemm_impl, 2)
     print("%s teacher-forced: max |dlogp| vocab %.3e, top-8 %.3e, top-1 agreement %d/%d" % (mode, worst, worst_top, agree, total))
-    assert worst_top <= 1e-2 and worst <= (1e-2 if mode == "bf16_f16" else 2e-2)
+    assert worst_top <= 1e-2 and worst <= (1e-2 if mode == "fp16" else 2e-2)
 
 
 def test_16bit_six_layer_decoder_error_and_stepwise_agreement():
     """Same protocol on the 6-layer decoder of the headline config; per-row-step top-1 agreement >= 99 % for the
     production mode (bf16 weights x fp16 activations)."""
-    for mode in ("bf16", "bf16_f16"):
+    for mode in ("bf16", "fp16"):
         worst, worst_top, agree, total = _teacher_forced(mode, _lib.GEMM_AUTO, 6, seed=43, V=8000, B=12, S=20)
         print("6-layer %s: max |dlogp| vocab %.3e, top-8 %.3e, top-1 agreement %d/%d = %.4f" % (
             mode, worst, worst_top, agree, total, agree / total))
         assert worst_top <= 1e-2
-        if mode == "bf16_f16":
+        if mode == "fp16":
             assert agree >= 0.99 * total
 
 
-@pytest.mark.parametrize("mode", ["bf16", "bf16_f16"])
+@pytest.mark.parametrize("mode", ["bf16", "fp16"])
 def test_16bit_free_running_token_agreement(mode):
     """Free-running agreement with the fp32 oracle (whole sequences; one early flip changes every later token).
     Random-init models have top-1/top-2 gaps of ~0.1 nats (p10 ~0.01), so this is reported, with a loose floor."""

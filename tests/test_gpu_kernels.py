@@ -46,14 +46,14 @@ def test_linear_bf16(impl, M, N, K):
 
 @pytest.mark.parametrize("impl", [_lib.GEMM_SIMT, _lib.GEMM_TCGEN05], ids=["simt", "tcgen05"])
 @pytest.mark.parametrize("M,N,K", [(32, 768, 768), (244, 3072, 768), (100, 768, 3072), (300, 1000, 768)])
-def test_linear_bf16_weights_fp16_activations(impl, M, N, K):
-    """mixed operand formats: UMMA-A = bf16 weights, UMMA-B = fp16 activations (ITB_BF16_F16)."""
-    A, W, b = _rand((M, K), 4, 1.0, torch.float16), _rand((N, K), 5, 0.05, torch.bfloat16), _rand((N,), 6)
+def test_linear_fp16(impl, M, N, K):
+    """ITB_F16: fp16 weights and activations (UMMA kind::f16 with both operand formats f16)."""
+    A, W, b = _rand((M, K), 4, 1.0, torch.float16), _rand((N, K), 5, 0.05, torch.float16), _rand((N,), 6)
     ref = A.double() @ W.double().t() + b.double()
-    out = linear(_lib.BF16_F16, impl, _lib.EPI_BIAS_F32, A, W, b)
+    out = linear(_lib.F16, impl, _lib.EPI_BIAS_F32, A, W, b)
     assert torch.isfinite(out).all()
     assert rel_err(out, ref) < 2e-5
-    out2 = linear(_lib.BF16_F16, impl, _lib.EPI_BIAS_GELU_ACT, A, W, b)
+    out2 = linear(_lib.F16, impl, _lib.EPI_BIAS_GELU_ACT, A, W, b)
     assert out2.dtype == torch.float16 and rel_err(out2.float(), torch.nn.functional.gelu(ref)) < 1e-3
 
 
@@ -65,7 +65,7 @@ def test_linear_tcgen05_back_to_back_is_deterministic():
 
 
 # ------------------------------------------------------------------------------------------------ LN kernels
-@pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16, _lib.BF16_F16])
+@pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16, _lib.F16])
 def test_embed_ln_and_add_ln(dtype):
     M, beam, d, T, V = 12, 4, 768, 9, 50
     step = 3
@@ -95,7 +95,7 @@ def test_embed_ln_and_add_ln(dtype):
 
 
 # ------------------------------------------------------------------------------------------------ attention
-@pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16, _lib.BF16_F16])
+@pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16, _lib.F16])
 @pytest.mark.parametrize("step", [1, 2, 40])
 def test_self_attention_through_ancestor_table(dtype, step):
     B, beam, d, H, T = 3, 4, 768, 12, 48
@@ -130,7 +130,7 @@ def test_self_attention_through_ancestor_table(dtype, step):
     assert (ctx.double() - ref).abs().max() < tol
 
 
-@pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16, _lib.BF16_F16])
+@pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16, _lib.F16])
 @pytest.mark.parametrize("masked", [False, True])
 def test_cross_attention_with_additive_mask(dtype, masked):
     B, beam, d, H, S, L, layer = 3, 4, 768, 12, 21, 2, 1
