@@ -12,7 +12,8 @@ LIB_PATH = os.path.join(_HERE, "libitb.so")
 F32, BF16, F16 = 0, 1, 2      # (weights, activations): (f32,f32) / (bf16,bf16) / (fp16,fp16); include/itb.h
 GEMM_AUTO, GEMM_SIMT, GEMM_TCGEN05 = 0, 1, 2
 EPI_BIAS_F32, EPI_BIAS_GELU_ACT, EPI_BIAS_ACT = 0, 1, 2
-ABI_VERSION = 1
+ABI_VERSION = 2
+Y_PARTIALS = 4
 
 P = C.c_void_p
 
@@ -45,7 +46,7 @@ _SIGS = {
     "itb_sizeof_layer": (C.c_int, []),
     "itb_linear": (C.c_int, [C.c_int, C.c_int, C.c_int, P, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, P]),
     "itb_embed_ln": (C.c_int, [C.c_int, P, P, P, P, P, P, P, P, C.c_float, P, P, C.c_int, C.c_int, C.c_int, C.c_int, P]),
-    "itb_add_ln": (C.c_int, [C.c_int, P, P, P, P, C.c_float, P, P, C.c_int, C.c_int, P]),
+    "itb_add_ln": (C.c_int, [C.c_int, P, P, C.c_int, P, P, C.c_float, P, P, C.c_int, C.c_int, P]),
     "itb_self_attention": (C.c_int, [C.c_int, P, P, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, P]),
     "itb_cross_attention": (C.c_int, [C.c_int, P, P, C.c_int, P, C.c_int, P, P, C.c_int, C.c_int, C.c_int, C.c_int,
                                       C.c_int, C.c_int, P]),
@@ -55,6 +56,8 @@ _SIGS = {
     "itb_decoder_create": (C.c_int, [C.POINTER(Config), C.POINTER(P)]),
     "itb_decoder_destroy": (C.c_int, [P]),
     "itb_decoder_step": (C.c_int, [P, P]),
+    "itb_decoder_capture": (C.c_int, [P, C.c_int]),
+    "itb_decoder_launch": (C.c_int, [P, P]),
     "itb_cross_kv": (C.c_int, [C.c_int, C.c_int, P, P, P, P, C.c_int, C.c_int, C.c_int, P]),
 }
 EXPORTS = tuple(sorted(_SIGS))

@@ -2,6 +2,7 @@
 #include <cuda.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 #include "common.cuh"
@@ -10,9 +11,9 @@
 int itb_gemm_simt(int dtype, int epi, const void* ctl, const void* A, const void* W, const float* bias, void* out,
                   int M, int N, int K, int ldo, cudaStream_t s);
 int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const void* ctl, const float* bias, void* out,
-                int M, int N, int K, int ldo, int act_f16, cudaStream_t s);
+                int M, int N, int K, int ldo, int act_f16, int mt, int nsplit, cudaStream_t s);
 int itb_make_tmap_16b(CUtensorMap* map, const void* base, int rows, int K, int box_rows, int is_f16);
-int itb_tc_pick_mt(int M);
+void itb_tc_plan(int M, int N, int K, int max_split, int* mt_out, int* split_out);
 
 static thread_local char g_err[512] = "";
 
@@ -32,6 +33,15 @@ int itb_check_launch(const char* what) {
     return 0;
 }
 
+bool itb_pdl_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("ITB_PDL");
+        v = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    return v != 0;
+}
+
 static bool use_tc(int dtype, int impl) {
     if (impl == ITB_GEMM_SIMT) return false;
     return dtype != ITB_F32;       // fp32 (parity mode) always runs on the CUDA cores
@@ -41,24 +51,28 @@ static bool use_tc(int dtype, int impl) {
 struct Linear {
     const void* W = nullptr; const float* bias = nullptr; const void* A = nullptr; void* out = nullptr;
     int M = 0, N = 0, K = 0, ldo = 0, epi = 0;
+    int max_split = 1;       // > 1: `out` is [max_split][M][ldo] and the consumer sums `nsplit` partial outputs
+    int mt = 32, nsplit = 1;
     bool tc = false;
     CUtensorMap tmW, tmA;
     int prepare(int dtype, int impl) {
         tc = use_tc(dtype, impl);
         if (!tc) return 0;
+        itb_tc_plan(M, N, K, max_split, &mt, &nsplit);
         int r = itb_make_tmap_16b(&tmW, W, N, K, 128, dtype == ITB_F16 ? 1 : 0);
         if (r != 0) return r;
-        return itb_make_tmap_16b(&tmA, A, M, K, itb_tc_pick_mt(M), dtype == ITB_F16 ? 1 : 0);
+        return itb_make_tmap_16b(&tmA, A, M, K, mt, dtype == ITB_F16 ? 1 : 0);
     }
     int run(int dtype, const void* ctl, cudaStream_t s) const {
-        if (tc) return itb_gemm_tc(epi, &tmW, &tmA, ctl, bias, out, M, N, K, ldo, dtype == ITB_F16 ? 1 : 0, s);
+        if (tc) return itb_gemm_tc(epi, &tmW, &tmA, ctl, bias, out, M, N, K, ldo, dtype == ITB_F16 ? 1 : 0, mt, nsplit, s);
         return itb_gemm_simt(dtype, epi, ctl, A, W, bias, out, M, N, K, ldo, s);
     }
 };
 
-static Linear make_linear(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int ldo, int epi) {
+static Linear make_linear(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int ldo, int epi,
+                          int max_split = 1) {
     Linear l;
-    l.A = A; l.W = W; l.bias = bias; l.out = out; l.M = M; l.N = N; l.K = K; l.ldo = ldo; l.epi = epi;
+    l.A = A; l.W = W; l.bias = bias; l.out = out; l.M = M; l.N = N; l.K = K; l.ldo = ldo; l.epi = epi; l.max_split = max_split;
     return l;
 }
 
@@ -67,6 +81,9 @@ struct itb_decoder {
     std::vector<itb_layer> layers;
     std::vector<Linear> qkv, o, cq, co, f1, f2;
     Linear vocab;
+    cudaGraphExec_t exec = nullptr;      // `graph_steps` search steps captured once, replayed for the whole batch
+    int graph_steps = 0;
+    cudaStream_t cap_stream = nullptr;
 };
 
 extern "C" {
@@ -108,11 +125,11 @@ int itb_decoder_create(const itb_config* c, itb_decoder** out) {
     for (int l = 0; l < c->L && r == 0; ++l) {
         const itb_layer& w = d->layers[l];
         d->qkv.push_back(make_linear(c->x_act, w.w_qkv, w.b_qkv, c->qkv, M, 3 * D, D, 3 * D, ITB_EPI_BIAS_F32));
-        d->o.push_back(make_linear(c->ctx, w.w_o, w.b_o, c->y, M, D, D, D, ITB_EPI_BIAS_F32));
+        d->o.push_back(make_linear(c->ctx, w.w_o, w.b_o, c->y, M, D, D, D, ITB_EPI_BIAS_F32, ITB_Y_PARTIALS));
         d->cq.push_back(make_linear(c->x_act, w.w_cq, w.b_cq, c->qkv, M, D, D, 3 * D, ITB_EPI_BIAS_F32));
-        d->co.push_back(make_linear(c->ctx, w.w_co, w.b_co, c->y, M, D, D, D, ITB_EPI_BIAS_F32));
+        d->co.push_back(make_linear(c->ctx, w.w_co, w.b_co, c->y, M, D, D, D, ITB_EPI_BIAS_F32, ITB_Y_PARTIALS));
         d->f1.push_back(make_linear(c->x_act, w.w_1, w.b_1, c->ffn_h, M, F, D, F, ITB_EPI_BIAS_GELU_ACT));
-        d->f2.push_back(make_linear(c->ffn_h, w.w_2, w.b_2, c->y, M, D, F, D, ITB_EPI_BIAS_F32));
+        d->f2.push_back(make_linear(c->ffn_h, w.w_2, w.b_2, c->y, M, D, F, D, ITB_EPI_BIAS_F32, ITB_Y_PARTIALS));
         Linear* ls[6] = {&d->qkv.back(), &d->o.back(), &d->cq.back(), &d->co.back(), &d->f1.back(), &d->f2.back()};
         for (int i = 0; i < 6 && r == 0; ++i) r = ls[i]->prepare(c->dtype, c->gemm_impl);
     }
@@ -126,6 +143,10 @@ int itb_decoder_create(const itb_config* c, itb_decoder** out) {
 }
 
 int itb_decoder_destroy(itb_decoder* dec) {
+    if (dec != nullptr) {
+        if (dec->exec != nullptr) cudaGraphExecDestroy(dec->exec);
+        if (dec->cap_stream != nullptr) cudaStreamDestroy(dec->cap_stream);
+    }
     delete dec;
     return 0;
 }
@@ -146,18 +167,52 @@ int itb_decoder_step(itb_decoder* dec, void* stream) {
         ITB_TRY(dec->qkv[l].run(c.dtype, c.ctl, s));
         ITB_TRY(itb_self_attention(c.dtype, c.ctl, c.qkv, kv_l, c.anc, c.ctx, M, c.beam, D, c.H, c.T_max, stream));
         ITB_TRY(dec->o[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, w.ln1_g, w.ln1_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
+        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->o[l].nsplit, w.ln1_g, w.ln1_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
         ITB_TRY(dec->cq[l].run(c.dtype, c.ctl, s));
         ITB_TRY(itb_cross_attention(c.dtype, c.ctl, c.qkv, 3 * D, c.cross_kv, l, c.src_mask, c.ctx, M, c.beam, D, c.H,
                                     c.S, c.L, stream));
         ITB_TRY(dec->co[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, w.ln2_g, w.ln2_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
+        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->co[l].nsplit, w.ln2_g, w.ln2_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
         ITB_TRY(dec->f1[l].run(c.dtype, c.ctl, s));
         ITB_TRY(dec->f2[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, w.ln3_g, w.ln3_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
+        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->f2[l].nsplit, w.ln3_g, w.ln3_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
     }
     ITB_TRY(dec->vocab.run(c.dtype, c.ctl, s));
     ITB_TRY(itb_beam_step(&c, stream));
+    return 0;
+}
+
+// Captures `n_steps` consecutive search steps into one CUDA graph (the step index, ping-pong parity and the
+// termination flag live in device memory -- ItbCtl -- so the same graph serves every step of every batch of
+// this shape, and steps replayed past termination are no-ops).
+int itb_decoder_capture(itb_decoder* dec, int n_steps) {
+    ITB_REQUIRE(dec != nullptr && n_steps >= 1 && n_steps <= 64, "decoder_capture: bad arguments");
+    if (dec->exec != nullptr && dec->graph_steps == n_steps) return 0;
+    if (dec->exec != nullptr) { cudaGraphExecDestroy(dec->exec); dec->exec = nullptr; }
+    if (dec->cap_stream == nullptr) {
+        cudaError_t e = cudaStreamCreateWithFlags(&dec->cap_stream, cudaStreamNonBlocking);
+        if (e != cudaSuccess) { itb_set_error("decoder_capture: cudaStreamCreate: %s", cudaGetErrorString(e)); return -1; }
+    }
+    cudaError_t e = cudaStreamBeginCapture(dec->cap_stream, cudaStreamCaptureModeRelaxed);
+    if (e != cudaSuccess) { itb_set_error("decoder_capture: begin capture: %s", cudaGetErrorString(e)); return -1; }
+    int r = 0;
+    for (int i = 0; i < n_steps && r == 0; ++i) r = itb_decoder_step(dec, dec->cap_stream);
+    cudaGraph_t graph = nullptr;
+    e = cudaStreamEndCapture(dec->cap_stream, &graph);
+    if (r != 0) { if (graph != nullptr) cudaGraphDestroy(graph); return r; }
+    if (e != cudaSuccess || graph == nullptr) { itb_set_error("decoder_capture: end capture: %s", cudaGetErrorString(e)); return -1; }
+    e = cudaGraphInstantiate(&dec->exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) { dec->exec = nullptr; itb_set_error("decoder_capture: instantiate: %s", cudaGetErrorString(e)); return -1; }
+    dec->graph_steps = n_steps;
+    return 0;
+}
+
+// Replays the captured graph once (= graph_steps search steps) on `stream`.
+int itb_decoder_launch(itb_decoder* dec, void* stream) {
+    ITB_REQUIRE(dec != nullptr && dec->exec != nullptr, "decoder_launch: no captured graph (call itb_decoder_capture)");
+    cudaError_t e = cudaGraphLaunch(dec->exec, (cudaStream_t)stream);
+    if (e != cudaSuccess) { itb_set_error("decoder_launch: %s", cudaGetErrorString(e)); return -1; }
     return 0;
 }
 

@@ -1,209 +1,241 @@
 // Single-query attention for the incremental decoder step (head_dim fixed at 64 = 768/12,
-// reference src/lm_config.py:8,13).  One warp per (row, head):
-//   phase A  lane-per-position  q.k  (each lane streams one full 128/256-byte K row)
-//   phase B  warp softmax statistics in fp32 (exp(x-max)/sum, as torch.softmax)
-//   phase C  lane-per-dim       sum_p e_p * V[p]  (coalesced 128/256-byte V rows)
-// Self-attention reads the KV cache through the ancestor table written by the beam kernel, so a
-// beam reorder never copies K/V.  HBM-bound: 2*d*sizeof(T) bytes per (row, position, layer).
+// reference src/lm_config.py:8,13; HF BertSelfAttention).
+//
+// One CTA (4 warps) per (row, head) for self-attention and per (sentence, head, group of <=4 beam slots) for
+// cross-attention -- the beam slots of a sentence share the memory K/V, so each K/V byte is fetched once per group.
+// Positions are split over the warps in runs of 16; inside a warp 8 lanes x 16 B cover one 64-wide head row and
+// 4 positions are processed side by side, 4 such loads in flight per lane (64 positions per CTA iteration):
+//   phase A  scores  q.k/8 (+ additive -10000 source mask) -> shared memory
+//   phase B  softmax statistics in fp32: exp(x - max) / sum, as torch.softmax
+//   phase C  sum_p e_p * V[p], reduced over lanes, warps, then normalised and stored in the activation type.
+// Self-attention appends the row's new K,V to the cache first and reads the cache through the ancestor table
+// written by the beam kernel, so a beam reorder never copies K/V.  HBM-bound: 2*d*sizeof(T) bytes per
+// (row, position, layer) for self-attention, per (sentence, position, layer) for cross-attention.
 #include "common.cuh"
 #include "launch.h"
 
 #define DH 64
+#define AT_WARPS 4
+#define AT_THREADS (AT_WARPS * 32)
+#define NQ_MAX 4
 
-template <typename T> struct RowLoad;
-template <> struct RowLoad<float> {
-    static __device__ __forceinline__ float dot(const float* k, const float* q) {
-        const float4* k4 = reinterpret_cast<const float4*>(k);
-        float acc = 0.f;
-#pragma unroll
-        for (int j = 0; j < DH / 4; ++j) {
-            float4 v = k4[j];
-            acc = fmaf(v.x, q[4 * j + 0], acc);
-            acc = fmaf(v.y, q[4 * j + 1], acc);
-            acc = fmaf(v.z, q[4 * j + 2], acc);
-            acc = fmaf(v.w, q[4 * j + 3], acc);
-        }
-        return acc;
+template <typename T> struct Raw8;                       // 8 consecutive head dims of one K/V row
+template <> struct Raw8<float> {
+    float4 a, b;
+    __device__ __forceinline__ void load(const float* p) {
+        a = reinterpret_cast<const float4*>(p)[0];
+        b = reinterpret_cast<const float4*>(p)[1];
     }
-    static __device__ __forceinline__ float2 pair(const float* v, int lane) {
-        return reinterpret_cast<const float2*>(v)[lane];
+    __device__ __forceinline__ void unpack(float* o) const {
+        o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
     }
 };
-template <> struct RowLoad<__nv_bfloat16> {
-    static __device__ __forceinline__ float dot(const __nv_bfloat16* k, const float* q) {
-        const uint4* k4 = reinterpret_cast<const uint4*>(k);
-        float acc = 0.f;
+template <> struct Raw8<__nv_bfloat16> {
+    uint4 u;
+    __device__ __forceinline__ void load(const __nv_bfloat16* p) { u = *reinterpret_cast<const uint4*>(p); }
+    __device__ __forceinline__ void unpack(float* o) const {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
 #pragma unroll
-        for (int j = 0; j < DH / 8; ++j) {
-            uint4 u = k4[j];
-            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                float2 f = __bfloat1622float2(h[e]);
-                acc = fmaf(f.x, q[8 * j + 2 * e + 0], acc);
-                acc = fmaf(f.y, q[8 * j + 2 * e + 1], acc);
-            }
-        }
-        return acc;
+        for (int e = 0; e < 4; ++e) { float2 f = __bfloat1622float2(h[e]); o[2 * e] = f.x; o[2 * e + 1] = f.y; }
     }
-    static __device__ __forceinline__ float2 pair(const __nv_bfloat16* v, int lane) {
-        return __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(v)[lane]);
+};
+template <> struct Raw8<__half> {
+    uint4 u;
+    __device__ __forceinline__ void load(const __half* p) { u = *reinterpret_cast<const uint4*>(p); }
+    __device__ __forceinline__ void unpack(float* o) const {
+        const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { float2 f = __half22float2(h[e]); o[2 * e] = f.x; o[2 * e + 1] = f.y; }
     }
 };
 
-// Shared tail: softmax over sc[0..n) (+ optional extra current-position score) and P.V accumulation.
-template <> struct RowLoad<__half> {
-    static __device__ __forceinline__ float dot(const __half* k, const float* q) {
-        const uint4* k4 = reinterpret_cast<const uint4*>(k);
-        float acc = 0.f;
-#pragma unroll
-        for (int j = 0; j < DH / 8; ++j) {
-            uint4 u = k4[j];
-            const __half2* h = reinterpret_cast<const __half2*>(&u);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                float2 f = __half22float2(h[e]);
-                acc = fmaf(f.x, q[8 * j + 2 * e + 0], acc);
-                acc = fmaf(f.y, q[8 * j + 2 * e + 1], acc);
-            }
-        }
-        return acc;
-    }
-    static __device__ __forceinline__ float2 pair(const __half* v, int lane) {
-        return __half22float2(reinterpret_cast<const __half2*>(v)[lane]);
-    }
+struct AttnArgs {
+    const ItbCtl* ctl;
+    const float* q; int ldq;             // f32 queries, row stride ldq (self: the qkv buffer, k at +d, v at +2d)
+    void* kv;                            // self: cache of this layer [M][T_max][2][d]; cross: [B][S][L][2][d]
+    const unsigned char* anc;            // self: [2][M][T_max]
+    const unsigned char* mask;           // cross: [B][S] or null
+    void* ctx;                           // act [M][d]
+    int M, beam, d, T_max, S, L, layer;
 };
 
-template <typename T, typename VPtr>
-__device__ __forceinline__ void softmax_pv(float* sc, int n, bool has_cur, float s_cur, float2 v_cur, VPtr vptr,
-                                           int lane, float2& out) {
-    float mx = has_cur ? s_cur : -INFINITY;
-    for (int p = lane; p < n; p += 32) mx = fmaxf(mx, sc[p]);
-    mx = warp_max(mx);
-    float sum = 0.f;
-    for (int p = lane; p < n; p += 32) {
-        float e = expf(sc[p] - mx);
-        sc[p] = e;
-        sum += e;
-    }
-    sum = warp_sum(sum);
-    float e_cur = 0.f;
-    if (has_cur) { e_cur = expf(s_cur - mx); sum += e_cur; }
-    __syncwarp();
-    float ax = 0.f, ay = 0.f, bx = 0.f, by = 0.f;
-    int p = 0;
-    for (; p + 1 < n; p += 2) {
-        float2 v0 = RowLoad<T>::pair(vptr(p), lane);
-        float2 v1 = RowLoad<T>::pair(vptr(p + 1), lane);
-        float e0 = sc[p], e1 = sc[p + 1];
-        ax = fmaf(e0, v0.x, ax); ay = fmaf(e0, v0.y, ay);
-        bx = fmaf(e1, v1.x, bx); by = fmaf(e1, v1.y, by);
-    }
-    if (p < n) {
-        float2 v0 = RowLoad<T>::pair(vptr(p), lane);
-        float e0 = sc[p];
-        ax = fmaf(e0, v0.x, ax); ay = fmaf(e0, v0.y, ay);
-    }
-    if (has_cur) { ax = fmaf(e_cur, v_cur.x, ax); ay = fmaf(e_cur, v_cur.y, ay); }
-    float inv = 1.0f / sum;
-    out.x = (ax + bx) * inv;
-    out.y = (ay + by) * inv;
-}
-
-template <typename T, int HPC>
-__global__ void __launch_bounds__(HPC * 32) self_attn_kernel(const ItbCtl* __restrict__ ctl, const float* __restrict__ qkv,
-                                                             T* kv, const unsigned char* __restrict__ anc,
-                                                             T* __restrict__ ctx, int M, int beam, int d, int T_max) {
+// NQ query rows share the K/V rows addressed by `kaddr(p)` (V row = K row + d).
+template <typename T, int NQ, bool SELF>
+__global__ void __launch_bounds__(AT_THREADS) attn_kernel(AttnArgs a) {
     extern __shared__ float sm[];
-    if (ctl->done) return;
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int r = blockIdx.x, h = blockIdx.y * HPC + w;
-    const int pc = ctl->step - 1;                    // position of the new token; attends to 0..pc
-    float* qs = sm + w * DH;
-    float* sc = sm + HPC * DH + w * T_max;
-    const float* qrow = qkv + (size_t)r * 3 * d + h * DH;
-    // new K,V rounded to the cache type, appended at (row r, position pc)
-    float2 q2 = reinterpret_cast<const float2*>(qrow)[lane];
-    float2 k2 = reinterpret_cast<const float2*>(qrow + d)[lane];
-    float2 v2 = reinterpret_cast<const float2*>(qrow + 2 * d)[lane];
-    T kx = from_f32<T>(k2.x), ky = from_f32<T>(k2.y), vx = from_f32<T>(v2.x), vy = from_f32<T>(v2.y);
-    T* knew = kv + (((size_t)r * T_max + pc) * 2) * d + h * DH;
-    knew[2 * lane] = kx; knew[2 * lane + 1] = ky;
-    knew[d + 2 * lane] = vx; knew[d + 2 * lane + 1] = vy;
-    qs[2 * lane] = q2.x; qs[2 * lane + 1] = q2.y;
-    float s_cur = warp_sum(q2.x * to_f32<T>(kx) + q2.y * to_f32<T>(ky)) * 0.125f;
-    __syncwarp();
-    const unsigned char* arow = anc + ((size_t)ctl->cur * M + r) * T_max;
-    const int base = (r / beam) * beam;
-    for (int p = lane; p < pc; p += 32) {
-        const T* k = kv + (((size_t)(base + arow[p]) * T_max + p) * 2) * d + h * DH;
-        sc[p] = RowLoad<T>::dot(k, qs) * 0.125f;
-    }
-    __syncwarp();
-    float2 o;
-    auto vptr = [&](int p) { return kv + (((size_t)(base + arow[p]) * T_max + p) * 2 + 1) * d + h * DH; };
-    softmax_pv<T>(sc, pc, true, s_cur, make_float2(to_f32<T>(vx), to_f32<T>(vy)), vptr, lane, o);
-    T* orow = ctx + (size_t)r * d + h * DH;
-    orow[2 * lane] = from_f32<T>(o.x);
-    orow[2 * lane + 1] = from_f32<T>(o.y);
-}
-
-template <typename T, int HPC>
-__global__ void __launch_bounds__(HPC * 32) cross_attn_kernel(const ItbCtl* __restrict__ ctl, const float* __restrict__ q,
-                                                              int ldq, const T* __restrict__ ckv, int layer,
-                                                              const unsigned char* __restrict__ mask,
-                                                              T* __restrict__ ctx, int M, int beam, int d, int S, int L) {
-    extern __shared__ float sm[];
+    pdl_trigger();
+    pdl_wait();
+    const ItbCtl* ctl = a.ctl;
     if (ctl != nullptr && ctl->done) return;
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int r = blockIdx.x, h = blockIdx.y * HPC + w;
-    const int b = r / beam;
-    float* qs = sm + w * DH;
-    float* sc = sm + HPC * DH + w * S;
-    float2 q2 = reinterpret_cast<const float2*>(q + (size_t)r * ldq + h * DH)[lane];
-    qs[2 * lane] = q2.x; qs[2 * lane + 1] = q2.y;
-    __syncwarp();
-    const size_t pos_stride = (size_t)L * 2 * d;
-    const T* kbase = ckv + ((size_t)b * S * L + layer) * 2 * d + h * DH;
-    for (int p = lane; p < S; p += 32) {
-        float s = RowLoad<T>::dot(kbase + p * pos_stride, qs) * 0.125f;
-        // additive mask (1 - m) * -10000 : reference src/bert_seq2seq.py:36-37
-        if (mask != nullptr && mask[(size_t)b * S + p] == 0) s += -10000.0f;
-        sc[p] = s;
+    const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, g = lane >> 3, j = lane & 7;
+    const int h = blockIdx.y, d = a.d;
+    int n, row0, nq;
+    const T* kbase;
+    size_t pos_stride;
+    const unsigned char* arow = nullptr;
+    if (SELF) {
+        const int r = blockIdx.x;
+        row0 = r; nq = 1;
+        const int pc = ctl->step - 1;                    // position of the new token; attends to 0..pc
+        n = pc + 1;
+        kbase = reinterpret_cast<const T*>(a.kv) + h * DH;
+        pos_stride = (size_t)2 * d;
+        arow = a.anc + ((size_t)ctl->cur * a.M + r) * a.T_max;
+    } else {
+        const int b = blockIdx.x, q0 = blockIdx.z * NQ;
+        row0 = b * a.beam + q0; nq = min(NQ, a.beam - q0);
+        n = a.S;
+        kbase = reinterpret_cast<const T*>(a.kv) + ((size_t)b * a.S * a.L + a.layer) * 2 * d + h * DH;
+        pos_stride = (size_t)a.L * 2 * d;
     }
-    __syncwarp();
-    float2 o;
-    auto vptr = [&](int p) { return kbase + p * pos_stride + d; };
-    softmax_pv<T>(sc, S, false, 0.f, make_float2(0.f, 0.f), vptr, lane, o);
-    T* orow = ctx + (size_t)r * d + h * DH;
-    orow[2 * lane] = from_f32<T>(o.x);
-    orow[2 * lane + 1] = from_f32<T>(o.y);
-}
+    const int npad = (n + 3) & ~3;
+    float* sc = sm;                                      // [NQ][npad]
+    float* pv = sm + NQ * npad;                          // [AT_WARPS][NQ][DH]
+    float* inv = pv + AT_WARPS * NQ * DH;                // [NQ]
+    unsigned char* s_anc = reinterpret_cast<unsigned char*>(inv + NQ);     // SELF: [n] physical beam slot per position
 
-static int pick_hpc(int H) { return (H % 4 == 0) ? 4 : ((H % 2 == 0) ? 2 : 1); }
+    if (SELF) {
+        // append this row's K,V (rounded to the cache type) at position pc, then treat it like any cached position
+        const int r = row0, pc = n - 1;
+        T* knew = reinterpret_cast<T*>(a.kv) + (((size_t)r * a.T_max + pc) * 2) * d + h * DH;
+        const float* qrow = a.q + (size_t)r * a.ldq + h * DH;
+        if (tid < DH) knew[tid] = from_f32<T>(qrow[d + tid]);
+        else knew[d + tid - DH] = from_f32<T>(qrow[2 * d + tid - DH]);
+        for (int p = tid; p < pc; p += AT_THREADS) s_anc[p] = arow[p];
+        if (tid == 0) s_anc[pc] = (unsigned char)(r % a.beam);
+        __syncthreads();
+    }
+    const int base = SELF ? (row0 / a.beam) * a.beam : 0;
+    auto kaddr = [&](int p) -> const T* {
+        if (SELF) return kbase + ((size_t)(base + s_anc[p]) * a.T_max + p) * pos_stride + j * 8;
+        return kbase + (size_t)p * pos_stride + j * 8;
+    };
+
+    // queries: this lane's 8 dims, pre-scaled by 1/sqrt(64) (exact: power of two)
+    float qr[NQ][8];
+#pragma unroll
+    for (int qi = 0; qi < NQ; ++qi) {
+        const int r = row0 + min(qi, nq - 1);
+        const float4* q4 = reinterpret_cast<const float4*>(a.q + (size_t)r * a.ldq + h * DH + j * 8);
+        float4 x = q4[0], y = q4[1];
+        qr[qi][0] = x.x * 0.125f; qr[qi][1] = x.y * 0.125f; qr[qi][2] = x.z * 0.125f; qr[qi][3] = x.w * 0.125f;
+        qr[qi][4] = y.x * 0.125f; qr[qi][5] = y.y * 0.125f; qr[qi][6] = y.z * 0.125f; qr[qi][7] = y.w * 0.125f;
+    }
+
+    // ---- phase A: scores ----
+    for (int p0 = w * 16; p0 < n; p0 += AT_WARPS * 16) {
+        Raw8<T> raw[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int p = p0 + u * 4 + g;
+            if (p < n) raw[u].load(kaddr(p));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int p = p0 + u * 4 + g;
+            float kf[8];
+            if (p < n) raw[u].unpack(kf);
+            else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) kf[e] = 0.f;
+            }
+#pragma unroll
+            for (int qi = 0; qi < NQ; ++qi) {
+                float acc = 0.f;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc = fmaf(kf[e], qr[qi][e], acc);
+                acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+                acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+                acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+                if (j == 0 && p < n) {
+                    // additive mask (1 - m) * -10000 : reference src/bert_seq2seq.py:36-37
+                    if (!SELF && a.mask != nullptr && a.mask[(size_t)blockIdx.x * a.S + p] == 0) acc += -10000.0f;
+                    sc[qi * npad + p] = acc;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    // ---- phase B: softmax statistics, one warp per query ----
+    for (int qi = w; qi < NQ; qi += AT_WARPS) {
+        float* s = sc + qi * npad;
+        float mx = -INFINITY;
+        for (int p = lane; p < n; p += 32) mx = fmaxf(mx, s[p]);
+        mx = warp_max(mx);
+        float sum = 0.f;
+        for (int p = lane; p < n; p += 32) {
+            float e = expf(s[p] - mx);
+            s[p] = e;
+            sum += e;
+        }
+        sum = warp_sum(sum);
+        if (lane == 0) inv[qi] = 1.0f / sum;
+    }
+    __syncthreads();
+    // ---- phase C: P.V ----
+    float acc[NQ][8];
+#pragma unroll
+    for (int qi = 0; qi < NQ; ++qi)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[qi][e] = 0.f;
+    for (int p0 = w * 16; p0 < n; p0 += AT_WARPS * 16) {
+        Raw8<T> raw[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int p = p0 + u * 4 + g;
+            if (p < n) raw[u].load(kaddr(p) + d);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int p = p0 + u * 4 + g;
+            if (p < n) {
+                float vf[8];
+                raw[u].unpack(vf);
+#pragma unroll
+                for (int qi = 0; qi < NQ; ++qi) {
+                    const float e = sc[qi * npad + p];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[qi][k] = fmaf(e, vf[k], acc[qi][k]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int qi = 0; qi < NQ; ++qi)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            float v = acc[qi][k];
+            v += __shfl_xor_sync(0xffffffffu, v, 8);
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            if (g == 0) pv[(w * NQ + qi) * DH + j * 8 + k] = v;
+        }
+    __syncthreads();
+    for (int i = tid; i < nq * DH; i += AT_THREADS) {
+        const int qi = i / DH, k = i % DH;
+        float v = 0.f;
+#pragma unroll
+        for (int ww = 0; ww < AT_WARPS; ++ww) v += pv[(ww * NQ + qi) * DH + k];
+        reinterpret_cast<T*>(a.ctx)[(size_t)(row0 + qi) * d + h * DH + k] = from_f32<T>(v * inv[qi]);
+    }
+}
 
 template <typename T>
-static int launch_self(const ItbCtl* ctl, const float* qkv, void* kv, const unsigned char* anc, void* ctx, int M,
-                       int beam, int d, int H, int T_max, cudaStream_t s) {
-    int hpc = pick_hpc(H);
-    size_t smem = (size_t)hpc * (DH + T_max) * sizeof(float);
-    dim3 grid(M, H / hpc);
-    if (hpc == 4) self_attn_kernel<T, 4><<<grid, 128, smem, s>>>(ctl, qkv, (T*)kv, anc, (T*)ctx, M, beam, d, T_max);
-    else if (hpc == 2) self_attn_kernel<T, 2><<<grid, 64, smem, s>>>(ctl, qkv, (T*)kv, anc, (T*)ctx, M, beam, d, T_max);
-    else self_attn_kernel<T, 1><<<grid, 32, smem, s>>>(ctl, qkv, (T*)kv, anc, (T*)ctx, M, beam, d, T_max);
+static int launch_self(const AttnArgs& a, int H, cudaStream_t s) {
+    const size_t smem = ((size_t)((a.T_max + 3) & ~3) + AT_WARPS * DH + 1) * sizeof(float) + a.T_max + 16;
+    cudaError_t e = itb_launch(attn_kernel<T, 1, true>, dim3(a.M, H), dim3(AT_THREADS), smem, s, a);
+    if (e != cudaSuccess) { itb_set_error("self_attention: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("self_attention");
 }
 
 template <typename T>
-static int launch_cross(const ItbCtl* ctl, const float* q, int ldq, const void* ckv, int layer,
-                        const unsigned char* mask, void* ctx, int M, int beam, int d, int H, int S, int L,
-                        cudaStream_t s) {
-    int hpc = pick_hpc(H);
-    size_t smem = (size_t)hpc * (DH + S) * sizeof(float);
-    dim3 grid(M, H / hpc);
-    if (hpc == 4) cross_attn_kernel<T, 4><<<grid, 128, smem, s>>>(ctl, q, ldq, (const T*)ckv, layer, mask, (T*)ctx, M, beam, d, S, L);
-    else if (hpc == 2) cross_attn_kernel<T, 2><<<grid, 64, smem, s>>>(ctl, q, ldq, (const T*)ckv, layer, mask, (T*)ctx, M, beam, d, S, L);
-    else cross_attn_kernel<T, 1><<<grid, 32, smem, s>>>(ctl, q, ldq, (const T*)ckv, layer, mask, (T*)ctx, M, beam, d, S, L);
+static int launch_cross(const AttnArgs& a, int H, cudaStream_t s) {
+    const size_t smem = ((size_t)NQ_MAX * ((a.S + 3) & ~3) + AT_WARPS * NQ_MAX * DH + NQ_MAX) * sizeof(float) + 16;
+    const int B = a.M / a.beam;
+    cudaError_t e;
+    if (a.beam == 1) e = itb_launch(attn_kernel<T, 1, false>, dim3(B, H, 1), dim3(AT_THREADS), smem, s, a);
+    else if (a.beam == 2) e = itb_launch(attn_kernel<T, 2, false>, dim3(B, H, 1), dim3(AT_THREADS), smem, s, a);
+    else e = itb_launch(attn_kernel<T, NQ_MAX, false>, dim3(B, H, (a.beam + NQ_MAX - 1) / NQ_MAX), dim3(AT_THREADS), smem, s, a);
+    if (e != cudaSuccess) { itb_set_error("cross_attention: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("cross_attention");
 }
 
@@ -213,10 +245,13 @@ int itb_self_attention(int dtype, const itb_ctl* ctl, const float* qkv, void* kv
                        void* ctx, int M, int beam, int d, int H, int T_max, void* stream) {
     ITB_REQUIRE(d == H * DH, "self_attention: head_dim must be 64 (d == 64*H)");
     ITB_REQUIRE(T_max <= 2048, "self_attention: T_max too large for the shared-memory score buffer");
-    const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
-    if (dtype == ITB_BF16) return launch_self<__nv_bfloat16>(c, qkv, kv_layer, anc, ctx, M, beam, d, H, T_max, (cudaStream_t)stream);
-    if (dtype == ITB_F16) return launch_self<__half>(c, qkv, kv_layer, anc, ctx, M, beam, d, H, T_max, (cudaStream_t)stream);
-    return launch_self<float>(c, qkv, kv_layer, anc, ctx, M, beam, d, H, T_max, (cudaStream_t)stream);
+    AttnArgs a = {};
+    a.ctl = reinterpret_cast<const ItbCtl*>(ctl);
+    a.q = qkv; a.ldq = 3 * d; a.kv = kv_layer; a.anc = anc; a.ctx = ctx;
+    a.M = M; a.beam = beam; a.d = d; a.T_max = T_max;
+    if (dtype == ITB_BF16) return launch_self<__nv_bfloat16>(a, H, (cudaStream_t)stream);
+    if (dtype == ITB_F16) return launch_self<__half>(a, H, (cudaStream_t)stream);
+    return launch_self<float>(a, H, (cudaStream_t)stream);
 }
 
 int itb_cross_attention(int dtype, const itb_ctl* ctl, const float* q, int ldq, const void* cross_kv, int layer,
@@ -224,10 +259,14 @@ int itb_cross_attention(int dtype, const itb_ctl* ctl, const float* q, int ldq, 
                         void* stream) {
     ITB_REQUIRE(d == H * DH, "cross_attention: head_dim must be 64 (d == 64*H)");
     ITB_REQUIRE(S <= 2048, "cross_attention: S too large for the shared-memory score buffer");
-    const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
-    if (dtype == ITB_BF16) return launch_cross<__nv_bfloat16>(c, q, ldq, cross_kv, layer, src_mask, ctx, M, beam, d, H, S, L, (cudaStream_t)stream);
-    if (dtype == ITB_F16) return launch_cross<__half>(c, q, ldq, cross_kv, layer, src_mask, ctx, M, beam, d, H, S, L, (cudaStream_t)stream);
-    return launch_cross<float>(c, q, ldq, cross_kv, layer, src_mask, ctx, M, beam, d, H, S, L, (cudaStream_t)stream);
+    ITB_REQUIRE(M % beam == 0, "cross_attention: M must be a multiple of the beam width");
+    AttnArgs a = {};
+    a.ctl = reinterpret_cast<const ItbCtl*>(ctl);
+    a.q = q; a.ldq = ldq; a.kv = const_cast<void*>(cross_kv); a.mask = src_mask; a.ctx = ctx;
+    a.M = M; a.beam = beam; a.d = d; a.S = S; a.L = L; a.layer = layer;
+    if (dtype == ITB_BF16) return launch_cross<__nv_bfloat16>(a, H, (cudaStream_t)stream);
+    if (dtype == ITB_F16) return launch_cross<__half>(a, H, (cudaStream_t)stream);
+    return launch_cross<float>(a, H, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -56,13 +56,17 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     __shared__ float s_val[8 * KT > 16 * 16 ? 8 * KT : 16 * 16];   // phase 1: per-warp lists; phase 2: row candidates
     __shared__ int s_idx[8 * KT > 16 * 16 ? 8 * KT : 16 * 16];
     __shared__ float s_m[8], s_s[8];
-    __shared__ float s_pool_val[32 * KT];                          // phase 2: chunk candidates of one row
-    __shared__ int s_pool_idx[32 * KT];
+    __shared__ float s_pool_val[8][32 * KT];                       // phase 2: chunk candidates of one row per warp
+    __shared__ int s_pool_idx[8][32 * KT];
     __shared__ float s_top_val[16];
     __shared__ int s_top_idx[16];
+    __shared__ float s_rtop_val[8][16];
+    __shared__ int s_rtop_idx[8][16];
     __shared__ int s_src[16], s_word[16];
     __shared__ int s_last;
 
+    pdl_trigger();
+    pdl_wait();
     ItbCtl* ctl = a.ctl;
     if (ctl->done) return;
     const int step = ctl->step, cur = ctl->cur, nxt = cur ^ 1;
@@ -161,47 +165,44 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     const int nrows = first ? 1 : K;
     float* rc_val = s_val;      // [nrows][K] row candidates (sentence-level values)
     int* rc_idx = s_idx;
-    for (int kr = 0; kr < nrows; ++kr) {
+    // one warp per beam row, all rows of the sentence in flight at once (the critical path of the step ends here)
+    for (int kr = w; kr < nrows; kr += 8) {
         const int rr = b * a.beam + kr;
         const float sc = a.scores[(size_t)cur * M + rr];
-        float lp = 1.f;
-        if (K > 1) lp = powf((a.sizes[(size_t)cur * M + rr] + 6.0f) / 6.0f, a.alpha);     // seq_gen.py:43
+        const float sz = a.sizes[(size_t)cur * M + rr];
         const bool rz = (a.fin[(size_t)cur * M + rr] != 0) || lim;
-        __syncthreads();
+        float lp = 1.f;
+        if (K > 1) lp = powf((sz + 6.0f) / 6.0f, a.alpha);                                  // seq_gen.py:43
         if (rz) {
             // whole row is 0 => V exact ties at (score + 0)/lp; lowest flat index first
-            if (tid < K) {
+            if (lane < K) {
                 float cv = sc + 0.0f;
                 if (K > 1) cv = cv / lp;
-                rc_val[kr * K + tid] = cv;
-                rc_idx[kr * K + tid] = kr * V + tid;
+                rc_val[kr * K + lane] = cv;
+                rc_idx[kr * K + lane] = kr * V + lane;
             }
         } else {
             const int n = a.n_chunk * KT;
-            for (int i = tid; i < n; i += blockDim.x) {
-                s_pool_val[i] = __ldcg(a.cand_val + (size_t)rr * n + i);
-                s_pool_idx[i] = __ldcg(a.cand_idx + (size_t)rr * n + i);
+            float* pool_val = s_pool_val[w];
+            int* pool_idx = s_pool_idx[w];
+            for (int i = lane; i < n; i += 32) {
+                pool_val[i] = __ldcg(a.cand_val + (size_t)rr * n + i);
+                pool_idx[i] = __ldcg(a.cand_idx + (size_t)rr * n + i);
             }
-            __syncthreads();
-            if (w == 0) {
-                float mm = -INFINITY, ss = 0.f;
-                for (int j = lane; j < a.n_chunk; j += 32) mm = fmaxf(mm, __ldcg(a.chunk_max + (size_t)rr * a.n_chunk + j));
-                mm = warp_max(mm);
-                for (int j = lane; j < a.n_chunk; j += 32) {
-                    float cm = __ldcg(a.chunk_max + (size_t)rr * a.n_chunk + j);
-                    if (cm != -INFINITY) ss += __ldcg(a.chunk_sum + (size_t)rr * a.n_chunk + j) * expf(cm - mm);
-                }
-                ss = warp_sum(ss);
-                const float logz = logf(ss);
-                warp_select(s_pool_val, s_pool_idx, n, K, s_top_val, s_top_idx, lane);
-                if (lane < K) {
-                    // log_softmax as ATen computes it: (x - max) - log(sum exp(x - max))   (seq_gen.py:194)
-                    float lpz = (s_top_val[lane] - mm) - logz;
-                    float cv = sc + lpz;                                                    // :199 / :201
-                    if (K > 1) cv = cv / lp;
-                    rc_val[kr * K + lane] = cv;
-                    rc_idx[kr * K + lane] = kr * V + s_top_idx[lane];
-                }
+            const float cm = (lane < a.n_chunk) ? __ldcg(a.chunk_max + (size_t)rr * a.n_chunk + lane) : -INFINITY;   // n_chunk <= 32
+            const float cs = (lane < a.n_chunk) ? __ldcg(a.chunk_sum + (size_t)rr * a.n_chunk + lane) : 0.f;
+            const float mm = warp_max(cm);
+            const float ss = warp_sum((cm != -INFINITY) ? cs * expf(cm - mm) : 0.f);
+            const float logz = logf(ss);
+            __syncwarp();
+            warp_select(pool_val, pool_idx, n, K, s_rtop_val[w], s_rtop_idx[w], lane);
+            if (lane < K) {
+                // log_softmax as ATen computes it: (x - max) - log(sum exp(x - max))   (seq_gen.py:194)
+                float lpz = (s_rtop_val[w][lane] - mm) - logz;
+                float cv = sc + lpz;                                                        // :199 / :201
+                if (K > 1) cv = cv / lp;
+                rc_val[kr * K + lane] = cv;
+                rc_idx[kr * K + lane] = kr * V + s_rtop_idx[w][lane];
             }
         }
     }
@@ -278,11 +279,13 @@ int itb_beam_step(const itb_config* c, void* stream) {
     a.chunk_sum = c->chunk_sum; a.sent_counter = c->sent_counter;
     dim3 grid(c->n_chunk, c->B * c->beam);
     cudaStream_t s = (cudaStream_t)stream;
+    cudaError_t e;
     switch (kt_for(c->beam)) {
-        case 4: beam_step_kernel<4><<<grid, 256, 0, s>>>(a); break;
-        case 8: beam_step_kernel<8><<<grid, 256, 0, s>>>(a); break;
-        default: beam_step_kernel<16><<<grid, 256, 0, s>>>(a); break;
+        case 4: e = itb_launch(beam_step_kernel<4>, grid, dim3(256), (size_t)0, s, a); break;
+        case 8: e = itb_launch(beam_step_kernel<8>, grid, dim3(256), (size_t)0, s, a); break;
+        default: e = itb_launch(beam_step_kernel<16>, grid, dim3(256), (size_t)0, s, a); break;
     }
+    if (e != cudaSuccess) { itb_set_error("beam_step: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("beam_step");
 }
 

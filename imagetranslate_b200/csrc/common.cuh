@@ -22,6 +22,14 @@ struct ItbCtl {
     int pad_;
 };
 
+// Programmatic dependent launch (PDL).  Every kernel of the step chain is launched with the programmatic-stream-
+// serialization attribute: it may START while its predecessor is still running, executes only work that does not
+// depend on earlier kernels (barrier / TMEM set-up, weight-tile TMA loads), and calls pdl_wait() before touching
+// anything an earlier kernel wrote (or writing anything an earlier kernel reads).  pdl_wait() returns once the
+// predecessor grid has completed and flushed; pdl_trigger() lets the successor be scheduled.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

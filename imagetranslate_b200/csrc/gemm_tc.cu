@@ -90,7 +90,10 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
 
 template <int MT> struct TcCfg {
     static constexpr int kStageBytes = TC_BN * TC_BK * 2 + MT * TC_BK * 2;
-    static constexpr int kStagesRaw = (200 * 1024) / kStageBytes;
+    // small-MT tiles (latency-bound decode GEMMs) keep ~100 KB in flight so that two CTAs (the tail of one GEMM and
+    // the PDL-launched head of the next) can share an SM; large tiles take the whole SM.
+    static constexpr int kBudget = (MT <= 64 ? 100 : 200) * 1024;
+    static constexpr int kStagesRaw = kBudget / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kTmemCols = (2 * MT) < 32 ? 32 : (2 * MT);            // power of two for MT in {32,64,128,256}
     static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
@@ -100,10 +103,10 @@ template <int MT, int EPI>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
                const ItbCtl* __restrict__ ctl, const float* __restrict__ bias, void* __restrict__ out, int M, int N,
-               int K, int ldo, int act_f16) {
+               int K, int ldo, int act_f16, int nsplit, size_t part_stride) {
     using Cfg = TcCfg<MT>;
     extern __shared__ uint8_t smem_raw[];
-    if (ctl != nullptr && ctl->done) return;           // uniform early-out, before any barrier / TMEM allocation
+    pdl_trigger();                                     // the next kernel of the chain may start its own prologue
 
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* smem_w = smem;                                           // [stages][128][64] bf16, 1024-aligned
@@ -117,7 +120,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_tiles = (N + TC_BN - 1) / TC_BN, m_tiles = (M + MT - 1) / MT;
-    const int total = n_tiles * m_tiles, KB = K / TC_BK;
+    // split-K: tile t = ((nt * m_tiles) + mt) * nsplit + ks computes k-blocks [ks*KB, (ks+1)*KB) into partial output ks
+    const int total = n_tiles * m_tiles * nsplit, KB = K / TC_BK / nsplit;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmW)) : "memory");
@@ -137,20 +141,47 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // Weights never depend on earlier kernels: the producer starts streaming the first weight tiles BEFORE the
+    // programmatic-dependency wait, so the HBM latency of the weight stream hides behind the predecessor's tail.
+    int pre = 0;
+    if (warp == 0 && lane == 0 && (int)blockIdx.x < total) {
+        const int t = blockIdx.x, ks = t % nsplit, nt = (t / nsplit) / m_tiles;
+        pre = KB < Cfg::kStages ? KB : Cfg::kStages;
+        for (int kb = 0; kb < pre; ++kb) {
+            mbar_expect_tx(&full[kb], Cfg::kStageBytes);
+            tma_load_2d(smem_w + kb * (TC_BN * TC_BK * 2), &tmW, (ks * KB + kb) * TC_BK, nt * TC_BN, &full[kb]);
+        }
+    }
+    pdl_wait();                                        // activations / ctl are valid from here on
+    const bool done = (ctl != nullptr) && (ctl->done != 0);
+
     if (warp == 0) {
         if (lane == 0) {
-            uint32_t stage = 0, phase = 0;
-            for (int t = blockIdx.x; t < total; t += gridDim.x) {
-                const int nt = t / m_tiles, mt = t % m_tiles;
-                for (int kb = 0; kb < KB; ++kb) {
-                    mbar_wait(&empty[stage], phase ^ 1);
-                    mbar_expect_tx(&full[stage], Cfg::kStageBytes);
-                    tma_load_2d(smem_w + stage * (TC_BN * TC_BK * 2), &tmW, kb * TC_BK, nt * TC_BN, &full[stage]);
-                    tma_load_2d(smem_a + stage * (MT * TC_BK * 2), &tmA, kb * TC_BK, mt * MT, &full[stage]);
-                    if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+            if ((int)blockIdx.x < total) {
+                const int t = blockIdx.x, ks = t % nsplit, mt = (t / nsplit) % m_tiles;
+                for (int kb = 0; kb < pre; ++kb)
+                    tma_load_2d(smem_a + kb * (MT * TC_BK * 2), &tmA, (ks * KB + kb) * TC_BK, mt * MT, &full[kb]);
+                if (done)                              // search already terminated: drain the copies, then leave
+                    for (int kb = 0; kb < pre; ++kb) mbar_wait(&full[kb], 0);
+            }
+            if (!done) {
+                uint32_t stage = (pre == Cfg::kStages) ? 0 : pre, phase = (pre == Cfg::kStages) ? 1 : 0;
+                int kb0 = pre;
+                for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                    const int ks = t % nsplit, mt = (t / nsplit) % m_tiles, nt = (t / nsplit) / m_tiles;
+                    for (int kb = kb0; kb < KB; ++kb) {
+                        mbar_wait(&empty[stage], phase ^ 1);
+                        mbar_expect_tx(&full[stage], Cfg::kStageBytes);
+                        tma_load_2d(smem_w + stage * (TC_BN * TC_BK * 2), &tmW, (ks * KB + kb) * TC_BK, nt * TC_BN, &full[stage]);
+                        tma_load_2d(smem_a + stage * (MT * TC_BK * 2), &tmA, (ks * KB + kb) * TC_BK, mt * MT, &full[stage]);
+                        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+                    }
+                    kb0 = 0;
                 }
             }
         }
+    } else if (done) {
+        // nothing to compute
     } else if (warp == 1) {
         if (lane == 0) {
             // instruction descriptor: D=f32 (bit 4); UMMA-A (weights) @7 and UMMA-B (activations) @10: bf16 = 1, f16 = 0 -- the two
@@ -180,11 +211,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         const int q = warp & 3;                                 // TMEM lane quarter this warp may access
         uint32_t as = 0, aphase = 0;
         for (int t = blockIdx.x; t < total; t += gridDim.x) {
-            const int nt = t / m_tiles, mt = t % m_tiles;
+            const int ks = t % nsplit, mt = (t / nsplit) % m_tiles, nt = (t / nsplit) / m_tiles;
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
             const int n = nt * TC_BN + q * 32 + lane;
-            const float bv = (n < N && bias != nullptr) ? bias[n] : 0.f;
+            const float bv = (n < N && bias != nullptr && ks == 0) ? bias[n] : 0.f;
+            float* outp = reinterpret_cast<float*>(out) + (size_t)ks * part_stride;      // split-K partial (f32 epilogue only)
 #pragma unroll 1
             for (int c0 = 0; c0 < MT; c0 += 32) {
                 uint32_t v[32];
@@ -196,7 +228,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
                         const int m = mbase + j;
                         if (m < M) {
                             float x = __uint_as_float(v[j]) + bv;
-                            if (EPI == ITB_EPI_BIAS_F32) reinterpret_cast<float*>(out)[(size_t)m * ldo + n] = x;
+                            if (EPI == ITB_EPI_BIAS_F32) outp[(size_t)m * ldo + n] = x;
                             else {
                                 if (EPI == ITB_EPI_BIAS_GELU_ACT) x = gelu_erf(x);
                                 if (act_f16) reinterpret_cast<__half*>(out)[(size_t)m * ldo + n] = __float2half_rn(x);
@@ -252,7 +284,7 @@ int itb_make_tmap_16b(CUtensorMap* map, const void* base, int rows, int K, int b
     return 0;
 }
 
-int itb_tc_pick_mt(int M) { return M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256)); }
+
 
 static int num_sms() {
     static int n = 0;
@@ -265,38 +297,63 @@ static int num_sms() {
     return n;
 }
 
+// Tile plan.  The decode GEMMs are weight-streaming and latency-bound, so the activation rows per tile (UMMA N = mt)
+// and the split-K factor are chosen to spread the weight matrix over as many SMs as possible:
+//   cost = waves * (k-blocks per tile * bytes staged per k-block + a fixed per-tile overhead).
+// Split-K (partials summed by the consumer in a fixed order -> deterministic) only when the caller allows it.
+void itb_tc_plan(int M, int N, int K, int max_split, int* mt_out, int* split_out) {
+    const int n_tiles = (N + TC_BN - 1) / TC_BN, KB = K / TC_BK;
+    long best_cost = -1;
+    *mt_out = 32; *split_out = 1;
+    for (int mt = 32; mt <= 256; mt *= 2) {
+        for (int sp = 1; sp <= max_split; ++sp) {
+            if (KB % sp != 0) continue;
+            const long tiles = (long)n_tiles * ((M + mt - 1) / mt) * sp;
+            const long waves = (tiles + num_sms() - 1) / num_sms();
+            const long cost = waves * ((long)(KB / sp) * (TC_BN + mt) + 6 * 160);
+            if (best_cost < 0 || cost < best_cost) { *mt_out = mt; *split_out = sp; best_cost = cost; }
+        }
+        if (mt >= M) break;
+    }
+}
+
 template <int MT, int EPI>
 static int launch_tc(const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCtl* ctl, const float* bias, void* out,
-                     int M, int N, int K, int ldo, int act_f16, cudaStream_t s) {
+                     int M, int N, int K, int ldo, int act_f16, int nsplit, cudaStream_t s) {
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<MT>::kSmemBytes);
         if (e != cudaSuccess) { itb_set_error("gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return -1; }
         attr_set = true;
     }
-    const int total = ((N + TC_BN - 1) / TC_BN) * ((M + MT - 1) / MT);
+    const int total = ((N + TC_BN - 1) / TC_BN) * ((M + MT - 1) / MT) * nsplit;
     const int grid = total < num_sms() ? total : num_sms();
-    gemm_tc_kernel<MT, EPI><<<grid, TC_THREADS, TcCfg<MT>::kSmemBytes, s>>>(tmW, tmA, ctl, bias, out, M, N, K, ldo, act_f16);
+    cudaError_t e = itb_launch(gemm_tc_kernel<MT, EPI>, dim3(grid), dim3(TC_THREADS), (size_t)TcCfg<MT>::kSmemBytes, s, tmW, tmA,
+                               ctl, bias, out, M, N, K, ldo, act_f16, nsplit, (size_t)M * (size_t)ldo);
+    if (e != cudaSuccess) { itb_set_error("gemm_tc: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("gemm_tc");
 }
 
 template <int MT>
 static int launch_tc_epi(int epi, const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCtl* ctl, const float* bias,
-                         void* out, int M, int N, int K, int ldo, int act_f16, cudaStream_t s) {
-    if (epi == ITB_EPI_BIAS_F32) return launch_tc<MT, ITB_EPI_BIAS_F32>(tmW, tmA, ctl, bias, out, M, N, K, ldo, act_f16, s);
-    if (epi == ITB_EPI_BIAS_GELU_ACT) return launch_tc<MT, ITB_EPI_BIAS_GELU_ACT>(tmW, tmA, ctl, bias, out, M, N, K, ldo, act_f16, s);
-    return launch_tc<MT, ITB_EPI_BIAS_ACT>(tmW, tmA, ctl, bias, out, M, N, K, ldo, act_f16, s);
+                         void* out, int M, int N, int K, int ldo, int act_f16, int nsplit, cudaStream_t s) {
+    if (epi == ITB_EPI_BIAS_F32) return launch_tc<MT, ITB_EPI_BIAS_F32>(tmW, tmA, ctl, bias, out, M, N, K, ldo, act_f16, nsplit, s);
+    if (epi == ITB_EPI_BIAS_GELU_ACT) return launch_tc<MT, ITB_EPI_BIAS_GELU_ACT>(tmW, tmA, ctl, bias, out, M, N, K, ldo, act_f16, 1, s);
+    return launch_tc<MT, ITB_EPI_BIAS_ACT>(tmW, tmA, ctl, bias, out, M, N, K, ldo, act_f16, 1, s);
 }
 
-// tmW: [N][K] box 128 rows; tmA: [M][K] box itb_tc_pick_mt(M) rows.
+// tmW: [N][K] box 128 rows; tmA: [M][K] box `mt` rows; (mt, nsplit) from itb_tc_plan.  With nsplit > 1 (f32 epilogue
+// only) `out` receives nsplit partial outputs [nsplit][M][ldo]; the bias is added to partial 0.
 int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const void* ctl, const float* bias, void* out,
-                int M, int N, int K, int ldo, int act_f16, cudaStream_t s) {
+                int M, int N, int K, int ldo, int act_f16, int mt, int nsplit, cudaStream_t s) {
     ITB_REQUIRE(K % TC_BK == 0 && K >= TC_BK, "linear(tcgen05): K must be a multiple of 64");
+    ITB_REQUIRE(nsplit >= 1 && (K / TC_BK) % nsplit == 0 && (nsplit == 1 || epi == ITB_EPI_BIAS_F32), "linear(tcgen05): bad split-K factor");
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
-    switch (itb_tc_pick_mt(M)) {
-        case 32: return launch_tc_epi<32>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, s);
-        case 64: return launch_tc_epi<64>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, s);
-        case 128: return launch_tc_epi<128>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, s);
-        default: return launch_tc_epi<256>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, s);
+    switch (mt) {
+        case 32: return launch_tc_epi<32>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, nsplit, s);
+        case 64: return launch_tc_epi<64>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, nsplit, s);
+        case 128: return launch_tc_epi<128>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, nsplit, s);
+        case 256: return launch_tc_epi<256>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, nsplit, s);
+        default: itb_set_error("linear(tcgen05): unsupported tile height %d", mt); return -2;
     }
 }

@@ -32,6 +32,8 @@ __global__ void __launch_bounds__(256) embed_ln_kernel(const ItbCtl* __restrict_
     extern __shared__ float sm[];
     float* row = sm;
     float* red = sm + d;
+    pdl_trigger();
+    pdl_wait();
     if (ctl->done) return;
     const int r = blockIdx.x;
     const int p = ctl->step - 1;                     // 0-based position of the token consumed this step
@@ -53,17 +55,25 @@ __global__ void __launch_bounds__(256) embed_ln_kernel(const ItbCtl* __restrict_
 
 template <typename TA>
 __global__ void __launch_bounds__(256) add_ln_kernel(const ItbCtl* __restrict__ ctl, const float* __restrict__ y,
-                                                     const float* __restrict__ g, const float* __restrict__ b, float eps,
-                                                     float* __restrict__ x_f32, TA* __restrict__ x_act, int M, int d) {
+                                                     int n_partial, const float* __restrict__ g,
+                                                     const float* __restrict__ b, float eps, float* __restrict__ x_f32,
+                                                     TA* __restrict__ x_act, int M, int d) {
     extern __shared__ float sm[];
     float* row = sm;
     float* red = sm + d;
+    pdl_trigger();
+    pdl_wait();
     if (ctl != nullptr && ctl->done) return;
     const int r = blockIdx.x;
-    const float4* y4 = reinterpret_cast<const float4*>(y + (size_t)r * d);
     const float4* x4 = reinterpret_cast<const float4*>(x_f32 + (size_t)r * d);
     for (int i = threadIdx.x; i < d / 4; i += blockDim.x) {
-        float4 a = y4[i], c = x4[i];
+        // y = sum of the split-K partial outputs of the producing GEMM, in a fixed order (deterministic)
+        float4 a = reinterpret_cast<const float4*>(y + (size_t)r * d)[i];
+        for (int sp = 1; sp < n_partial; ++sp) {
+            float4 t = reinterpret_cast<const float4*>(y + ((size_t)sp * M + r) * d)[i];
+            a.x += t.x; a.y += t.y; a.z += t.z; a.w += t.w;
+        }
+        float4 c = x4[i];
         row[4 * i + 0] = a.x + c.x;
         row[4 * i + 1] = a.y + c.y;
         row[4 * i + 2] = a.z + c.z;
@@ -139,30 +149,36 @@ int itb_embed_ln(int dtype, const itb_ctl* ctl, const int* tokens, const int* tg
     size_t smem = (d + 32) * sizeof(float);
     cudaStream_t s = (cudaStream_t)stream;
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
+    cudaError_t e;
     if (dtype == ITB_BF16)
-        embed_ln_kernel<__nv_bfloat16><<<M, 256, smem, s>>>(c, tokens, tgt_lang, word, pos, type, g, b, eps, x_f32,
-                                                            (__nv_bfloat16*)x_act, M, beam, d, T_max);
+        e = itb_launch(embed_ln_kernel<__nv_bfloat16>, dim3(M), dim3(256), smem, s, c, tokens, tgt_lang, word, pos, type, g, b,
+                       eps, x_f32, (__nv_bfloat16*)x_act, M, beam, d, T_max);
     else if (dtype == ITB_F16)
-        embed_ln_kernel<__half><<<M, 256, smem, s>>>(c, tokens, tgt_lang, word, pos, type, g, b, eps, x_f32,
-                                                     (__half*)x_act, M, beam, d, T_max);
+        e = itb_launch(embed_ln_kernel<__half>, dim3(M), dim3(256), smem, s, c, tokens, tgt_lang, word, pos, type, g, b, eps,
+                       x_f32, (__half*)x_act, M, beam, d, T_max);
     else
-        embed_ln_kernel<float><<<M, 256, smem, s>>>(c, tokens, tgt_lang, word, pos, type, g, b, eps, x_f32,
-                                                    (float*)x_act, M, beam, d, T_max);
+        e = itb_launch(embed_ln_kernel<float>, dim3(M), dim3(256), smem, s, c, tokens, tgt_lang, word, pos, type, g, b, eps,
+                       x_f32, (float*)x_act, M, beam, d, T_max);
+    if (e != cudaSuccess) { itb_set_error("embed_ln: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("embed_ln");
 }
 
-int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, const float* g, const float* b, float eps,
+int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, int n_partial, const float* g, const float* b, float eps,
                float* x_f32, void* x_act, int M, int d, void* stream) {
     ITB_REQUIRE(d % 4 == 0 && M > 0, "add_ln: d must be a multiple of 4");
+    ITB_REQUIRE(n_partial >= 1, "add_ln: n_partial must be >= 1");
     size_t smem = (d + 32) * sizeof(float);
     cudaStream_t s = (cudaStream_t)stream;
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
+    cudaError_t e;
     if (dtype == ITB_BF16)
-        add_ln_kernel<__nv_bfloat16><<<M, 256, smem, s>>>(c, y, g, b, eps, x_f32, (__nv_bfloat16*)x_act, M, d);
+        e = itb_launch(add_ln_kernel<__nv_bfloat16>, dim3(M), dim3(256), smem, s, c, y, n_partial, g, b, eps, x_f32,
+                       (__nv_bfloat16*)x_act, M, d);
     else if (dtype == ITB_F16)
-        add_ln_kernel<__half><<<M, 256, smem, s>>>(c, y, g, b, eps, x_f32, (__half*)x_act, M, d);
+        e = itb_launch(add_ln_kernel<__half>, dim3(M), dim3(256), smem, s, c, y, n_partial, g, b, eps, x_f32, (__half*)x_act, M, d);
     else
-        add_ln_kernel<float><<<M, 256, smem, s>>>(c, y, g, b, eps, x_f32, (float*)x_act, M, d);
+        e = itb_launch(add_ln_kernel<float>, dim3(M), dim3(256), smem, s, c, y, n_partial, g, b, eps, x_f32, (float*)x_act, M, d);
+    if (e != cudaSuccess) { itb_set_error("add_ln: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("add_ln");
 }
 

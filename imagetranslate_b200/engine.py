@@ -24,6 +24,9 @@ def _lin(mod):
     return mod.weight.detach(), mod.bias.detach()
 
 
+_UID = [0]
+
+
 class PackedDecoder(object):
     """Device-resident weights of ONE decoder (+ its output layer) in kernel layout.
 
@@ -36,6 +39,8 @@ class PackedDecoder(object):
         act = _WT[dtype_code]       # weight dtype of every linear
         self.dtype_code = dtype_code
         self._src = []
+        _UID[0] += 1
+        self.uid = _UID[0]           # cache key of everything that holds raw pointers into these weights
 
         def f32(t):
             self._src.append(t)
@@ -95,17 +100,22 @@ class Workspace(object):
     def __init__(self, device):
         self.device = device
         self.buf = {}
+        self.generation = 0          # bumped whenever a buffer moves (cached decoders / graphs hold raw pointers)
 
     def get(self, name, numel, dtype):
         t = self.buf.get(name)
         if t is None or t.numel() < numel or t.dtype != dtype:
             t = torch.empty(max(int(numel), 1), dtype=dtype, device=self.device)
             self.buf[name] = t
+            self.generation += 1
         return t
 
 
 class DecodeEngine(object):
-    def __init__(self, device, dtype_code, gemm_impl=_lib.GEMM_AUTO, poll_every=16):
+    GRAPH_STEPS = 8          # search steps per CUDA-graph replay
+    MAX_CACHED = 48          # decoders (TMA descriptors + instantiated graph) kept per engine
+
+    def __init__(self, device, dtype_code, gemm_impl=_lib.GEMM_AUTO, poll_every=16, use_graph=True):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("imagetranslate_b200: the decode path runs on CUDA devices only (no CPU fallback)")
@@ -114,8 +124,38 @@ class DecodeEngine(object):
         self.poll_every = poll_every
         self.ws = Workspace(self.device)
         self.lib = _lib.lib()
+        self.use_graph = use_graph
         self.last_steps = 0
         self.launches_per_step = None
+        self._decoders = {}          # shape key -> itb_decoder* (C.c_void_p)
+        self._dec_generation = -1
+        self._ctl_host = [torch.empty(8, dtype=torch.int32).pin_memory() for _ in range(4)]
+
+    def _drop_decoders(self):
+        for dec in self._decoders.values():
+            self.lib.itb_decoder_destroy(dec)
+        self._decoders.clear()
+
+    def __del__(self):
+        try:
+            self._drop_decoders()
+        except Exception:
+            pass
+
+    def _decoder(self, key, cfg):
+        """itb_decoder for this (weights, shape): cached, because creating one encodes ~40 TMA descriptors and
+        capturing its graph costs about as much as a few search steps."""
+        if self._dec_generation != self.ws.generation:       # some workspace buffer moved: every cached pointer is stale
+            self._drop_decoders()
+            self._dec_generation = self.ws.generation
+        dec = self._decoders.get(key)
+        if dec is None:
+            if len(self._decoders) >= self.MAX_CACHED:
+                self.lib.itb_decoder_destroy(self._decoders.pop(next(iter(self._decoders))))
+            dec = C.c_void_p()
+            _lib.check(self.lib.itb_decoder_create(C.byref(cfg), C.byref(dec)), "decoder_create")
+            self._decoders[key] = dec
+        return dec
 
     def _config(self, pw, B, beam, S, T_max, pad, eos, alpha):
         ws, act, M = self.ws, _ACT[self.dtype_code], B * beam
@@ -139,12 +179,13 @@ class DecodeEngine(object):
             scores=ws.get("scores", 2 * M, f32), sizes=ws.get("sizes", 2 * M, f32), fin=ws.get("fin", 2 * M, u8),
             kv_self=ws.get("kv_self", pw.L * M * T_max * 2 * pw.d, act),
             x_f32=ws.get("x_f32", M * pw.d, f32), x_act=ws.get("x_act", M * pw.d, act), qkv=ws.get("qkv", M * 3 * pw.d, f32),
-            ctx=ws.get("ctx", M * pw.d, act), y=ws.get("y", M * pw.d, f32), ffn_h=ws.get("ffn_h", M * pw.F, act),
+            ctx=ws.get("ctx", M * pw.d, act), y=ws.get("y", _lib.Y_PARTIALS * M * pw.d, f32), ffn_h=ws.get("ffn_h", M * pw.F, act),
             logits=ws.get("logits", M * V4, f32), cand_val=ws.get("cand_val", M * n_chunk * KT, f32),
             cand_idx=ws.get("cand_idx", M * n_chunk * KT, i32), chunk_max=ws.get("chunk_max", M * n_chunk, f32),
             chunk_sum=ws.get("chunk_sum", M * n_chunk, f32), sent_counter=ws.get("sent_counter", B, i32))
         for k, v in t.items():
             setattr(c, k, v.data_ptr())
+        t["out_tok"], t["out_len"] = ws.get("out_tok", B * T_max, i32), ws.get("out_len", 2 * B + 8, i32)
         return c, t
 
     @torch.no_grad()
@@ -169,10 +210,29 @@ class DecodeEngine(object):
         _lib.check(lib.itb_cross_kv(self.dtype_code, self.gemm_impl, _lib.ptr(mem), _lib.ptr(pw.w_ckv), _lib.ptr(pw.b_ckv),
                                     _lib.ptr(t["cross_kv"]), B * S, pw.d, pw.L, stream), "cross_kv")
         _lib.check(lib.itb_init_state(C.byref(cfg), _lib.ptr(first), int(max_len), stream), "init_state")
-        dec = C.c_void_p()
-        _lib.check(lib.itb_decoder_create(C.byref(cfg), C.byref(dec)), "decoder_create")
-        try:
-            n_steps = max(int(max_len) - 1, 0)
+        key = (pw.uid, B, beam, S, T_max, src_mask is not None, pad, eos, float(alpha))
+        dec = self._decoder(key, cfg)
+        n_steps = max(int(max_len) - 1, 0)
+        if trace is None and self.use_graph and n_steps > 0:
+            # CUDA-graph replay, GRAPH_STEPS search steps per launch; the device-side ctl block carries the step index
+            # and the termination flag, so the host only peeks at ctl.done (asynchronously, two replays behind).
+            _lib.check(lib.itb_decoder_capture(dec, self.GRAPH_STEPS), "decoder_capture")
+            n_launch = -(-n_steps // self.GRAPH_STEPS)
+            pending = []
+            for i in range(n_launch):
+                _lib.check(lib.itb_decoder_launch(dec, stream), "decoder_launch")
+                if n_launch - i > 3:
+                    ev = torch.cuda.Event()
+                    hb = self._ctl_host[i % 4]
+                    hb.copy_(t["ctl"][:8], non_blocking=True)
+                    ev.record()
+                    pending.append((ev, hb))
+                    if len(pending) > 2:
+                        ev0, hb0 = pending.pop(0)
+                        ev0.synchronize()
+                        if int(hb0[1]) != 0:
+                            break
+        else:
             i = 0
             while i < n_steps:
                 if trace is not None:      # test hook: state BEFORE the step (forces a sync per step)
@@ -193,15 +253,13 @@ class DecodeEngine(object):
                 i += 1
                 if i % self.poll_every == 0 and i < n_steps and int(t["ctl"][1].item()) != 0:   # ctl.done
                     break
-            out_tok = self.ws.get("out_tok", B * T_max, torch.int32)
-            out_len = self.ws.get("out_len", 2 * B, torch.int32)
-            _lib.check(lib.itb_finalize(_lib.ptr(t["ctl"]), _lib.ptr(t["tokens"]), _lib.ptr(t["max_lens"]), eos,
-                                        _lib.ptr(out_tok), _lib.ptr(out_len), C.c_void_p(out_len.data_ptr() + 4 * B),
-                                        B, beam, T_max, stream), "finalize")
-            tok = out_tok[:B * T_max].view(B, T_max).cpu()
-            lens = out_len[:2 * B].cpu()
-            self.last_steps = int(t["ctl"][2].item())
-        finally:
-            lib.itb_decoder_destroy(dec)
+        out_tok, out_len = t["out_tok"], t["out_len"]
+        _lib.check(lib.itb_finalize(_lib.ptr(t["ctl"]), _lib.ptr(t["tokens"]), _lib.ptr(t["max_lens"]), eos,
+                                    _lib.ptr(out_tok), _lib.ptr(out_len), C.c_void_p(out_len.data_ptr() + 4 * B),
+                                    B, beam, T_max, stream), "finalize")
+        tok = out_tok[:B * T_max].view(B, T_max).cpu()
+        out_len[2 * B:2 * B + 8].copy_(t["ctl"][:8])
+        lens = out_len[:2 * B + 8].cpu()
+        self.last_steps = int(lens[2 * B + 2])
         self.launches_per_step = 2 + 11 * pw.L
-        return tok, lens[:B], lens[B:]
+        return tok, lens[:B], lens[B:2 * B]

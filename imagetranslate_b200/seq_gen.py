@@ -7,6 +7,9 @@ The search itself (decoder step, vocabulary projection, log-softmax, scoring, to
 termination) runs in CUDA kernels -- see include/itb.h.  The encoder memory still comes from the
 model's own `encode` (:96,99,106), exactly as in the reference.
 """
+import threading
+from concurrent.futures import ThreadPoolExecutor
+
 import torch
 import torch.nn as nn
 
@@ -44,6 +47,9 @@ class BeamDecoder(nn.Module):
         self.gemm_impl = gemm_impl
         self._engines = {}
         self._packed = {}
+        self._lane = threading.local()      # forward_many: which engine (workspace + stream) this thread drives
+        self._lock = threading.Lock()
+        self.kernel_launches = 0            # kernels enqueued by this decoder so far (bench.py's gpu_launches)
 
     def len_penalty(self, lengths: torch.Tensor):
         """reference src/seq_gen.py:37-44 (kept for callers; the kernels compute it on device)."""
@@ -60,14 +66,16 @@ class BeamDecoder(nn.Module):
         return _lib.F32 if weight.dtype == torch.float32 else _lib.F16
 
     def _engine(self, device, code):
-        key = (str(device), code)
-        if key not in self._engines:
-            self._engines[key] = DecodeEngine(device, code, self.gemm_impl)
-        return self._engines[key]
+        key = (str(device), code, getattr(self._lane, "idx", 0))
+        with self._lock:
+            if key not in self._engines:
+                self._engines[key] = DecodeEngine(device, code, self.gemm_impl)
+            return self._engines[key]
 
     def _weights(self, model, lang, code, device):
         key = (lang if model.lang_dec or not model.tie_embed else -1, code, str(device))
-        pw = self._packed.get(key)
+        with self._lock:
+            pw = self._packed.get(key)
         if pw is None or pw.stale():
             decoder = model.decoder[lang] if model.lang_dec else model.decoder
             out_layer = model.output_layer if ((not model.lang_dec) and model.tie_embed) else model.output_layer[lang]
@@ -144,6 +152,60 @@ class BeamDecoder(nn.Module):
         pw = self._weights(model, batch_lang, code, device)
         tok, lens, lens_full = eng.decode(pw, memory, mem_mask, first_tokens, tgt_langs, max_lens, max_len, beam_width,
                                           int(pad_idx), int(eos), float(self.len_penalty_ratio))
+        with self._lock:
+            self.kernel_launches += eng.last_steps * eng.launches_per_step + 4
         tok = tok.to(torch.int64)
         sel = lens if unpad_output else lens_full
         return [tok[r, :int(sel[r])].clone() for r in range(B)]
+
+    # ------------------------------------------------------------------ several batches in flight
+    def forward_many(self, batches, lanes: int = 4):
+        """Decodes a list of batches (each a dict of `forward` keyword arguments) and returns their outputs in order.
+
+        Every batch is decoded exactly as `forward` would (whole reference batches, never re-batched, so results do
+        not depend on `lanes`), but up to `lanes` batches are in flight on separate CUDA streams, each with its own
+        workspace / KV cache / captured step graph.  A single search step at the reference batch sizes is a chain of
+        ~70 short latency-bound kernels that leaves most SMs idle; independent batches fill them.  This replaces the
+        reference's one-thread-per-GPU `DataParallelModel` fan-out (src/parallel.py:70-148) on ONE device."""
+        batches = list(batches)
+        if lanes <= 1 or len(batches) <= 1:
+            return [self.forward(**kw) for kw in batches]
+        model = self.seq2seq_model.module if hasattr(self.seq2seq_model, "module") else self.seq2seq_model
+        device = model.encoder.embeddings.word_embeddings.weight.device
+        if device.type != "cuda":
+            raise RuntimeError("imagetranslate_b200.BeamDecoder needs the model on a CUDA device (no CPU fallback)")
+        lanes = min(lanes, len(batches))
+        if not hasattr(self, "_streams") or len(self._streams) < lanes:
+            self._streams = [torch.cuda.Stream(device=device) for _ in range(lanes)]
+            self._pool = ThreadPoolExecutor(max_workers=lanes)
+        # pack the weights once, on the calling thread, before the lanes start
+        wemb = model.encoder.embeddings.word_embeddings.weight
+        code = self._dtype_code(wemb)
+        for kw in batches:
+            tl = kw["tgt_langs"][0] if isinstance(kw["tgt_langs"], list) else kw["tgt_langs"]
+            self._weights(model, int(tl[0]), code, device)
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream(device))
+        results = [None] * len(batches)
+        nxt = [0]
+
+        def lane_main(idx):
+            self._lane.idx = idx
+            stream = self._streams[idx]
+            with torch.cuda.device(device), torch.cuda.stream(stream):
+                stream.wait_event(ready)
+                while True:
+                    with self._lock:
+                        i = nxt[0]
+                        nxt[0] += 1
+                    if i >= len(batches):
+                        break
+                    results[i] = self.forward(**batches[i])
+                done = torch.cuda.Event()
+                done.record(stream)
+            return done
+
+        futs = [self._pool.submit(lane_main, i) for i in range(lanes)]
+        for f in futs:
+            torch.cuda.current_stream(device).wait_event(f.result())     # re-raises a lane's RuntimeError
+        return results

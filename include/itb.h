@@ -21,7 +21,8 @@
 extern "C" {
 #endif
 
-#define ITB_ABI_VERSION 1
+#define ITB_ABI_VERSION 2
+#define ITB_Y_PARTIALS 4   /* cfg.y holds up to this many split-K partial outputs: [ITB_Y_PARTIALS][M][d] floats */
 /* dtype codes: (linear-weight type, activation / KV-cache type).  Accumulation, softmax, LayerNorm statistics,
  * logits and beam scores are always fp32. */
 enum { ITB_F32 = 0,        /* float weights,  float activations   (parity mode, CUDA cores)                 */
@@ -76,7 +77,7 @@ typedef struct {
   float* x_f32; void* x_act;                /* [M][d] residual stream and its act-typed copy               */
   float* qkv;                               /* [M][3d]                                                     */
   void* ctx;                                /* act [M][d]                                                  */
-  float* y;                                 /* [M][d]                                                      */
+  float* y;                                 /* [ITB_Y_PARTIALS][M][d] split-K partials of the d-wide GEMMs */
   void* ffn_h;                              /* act [M][F]                                                  */
   float* logits;                            /* [M][V]                                                      */
   float* cand_val; int* cand_idx;           /* [M][n_chunk][KT]                                            */
@@ -107,8 +108,9 @@ int itb_embed_ln(int dtype, const itb_ctl* ctl, const int* tokens, const int* tg
                  const float* pos, const float* type, const float* g, const float* b, float eps, float* x_f32,
                  void* x_act, int M, int beam, int d, int T_max, void* stream);
 
-/* x = LayerNorm(y + x) in place on x_f32, and act copy.  HF BertSelfOutput / BertOutput (A.4, A.6). */
-int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, const float* g, const float* b, float eps,
+/* x = LayerNorm(sum_{s<n_partial} y[s] + x) in place on x_f32, and act copy.  HF BertSelfOutput / BertOutput
+ * (A.4, A.6).  y is [n_partial][M][d]: the split-K partial outputs of the producing GEMM, summed in a fixed order. */
+int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, int n_partial, const float* g, const float* b, float eps,
                float* x_f32, void* x_act, int M, int d, void* stream);
 
 /* Single-query causal self-attention over the KV cache through the ancestor table; appends the
@@ -141,6 +143,11 @@ int itb_decoder_destroy(itb_decoder* dec);
 /* Enqueues one full search step i (embed -> L decoder layers -> vocab projection -> beam step).
  * Graph-capturable: the step index lives in cfg->ctl. */
 int itb_decoder_step(itb_decoder* dec, void* stream);
+/* Captures n_steps (1..64) consecutive itb_decoder_step()s into one CUDA graph owned by `dec`; itb_decoder_launch
+ * replays it on `stream`.  Steps replayed after the search terminated (seq_gen.py:134-136) are no-ops, so the host
+ * may over-enqueue and only has to look at ctl.done now and then (the reference synchronises every step). */
+int itb_decoder_capture(itb_decoder* dec, int n_steps);
+int itb_decoder_launch(itb_decoder* dec, void* stream);
 /* One-off per batch: cross K,V of all layers = memory[B*S][d] . Wckv[L*2d][d]^T + b  (HF BertSelfAttention
  * key/value on encoder_hidden_states; the reference redoes it every step: SURVEY K5). */
 int itb_cross_kv(int dtype, int impl, const void* memory, const void* w_ckv, const float* b_ckv, void* cross_kv,

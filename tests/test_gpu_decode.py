@@ -164,3 +164,25 @@ def test_16bit_free_running_token_agreement(mode):
         agree += sum(1 for a, b in zip(g.tolist(), w.tolist()) if a == b)
     print("%s free-running token agreement %d / %d = %.3f" % (mode, agree, total, agree / total))
     assert agree >= 0.5 * total
+
+
+@pytest.mark.parametrize("dtype", ["fp32", "bf16"])
+def test_forward_many_lanes_equal_sequential(dtype):
+    """Several batches in flight on separate streams (forward_many) give exactly the outputs of one-by-one forward
+    calls: batches are never merged or re-batched, and every kernel of the step is deterministic."""
+    model, _ = _fresh_case(61, 3000, 2, 8, 4, 2)
+    model = model.to(DEV)
+    batches = []
+    for i, (B, S) in enumerate([(5, 9), (3, 17), (8, 6), (2, 23), (6, 12), (4, 9), (7, 15)]):
+        src, mask, pad_idx = cases.make_text_batch(B, S, 3000, 100 + i)
+        batches.append(dict(src_inputs=src, src_mask=mask, src_sizes=pad_idx, src_langs=torch.zeros(B, dtype=torch.long),
+                            first_tokens=torch.full((B,), 6), tgt_langs=torch.ones(B, dtype=torch.long), pad_idx=0))
+    bd = BeamDecoder(model, beam_width=4, dtype=dtype, **cases.GEN)
+    with torch.no_grad():
+        seq = [bd(**kw) for kw in batches]
+        for lanes in (3, 4):
+            par = bd.forward_many(batches, lanes=lanes)
+            assert [[o.tolist() for o in b] for b in par] == [[o.tolist() for o in b] for b in seq]
+    if dtype == "fp32":
+        want = R.beam_search(model.cpu(), beam_width=4, **cases.GEN, **batches[1])
+        assert [o.tolist() for o in seq[1]] == [w.tolist() for w in want]

@@ -86,9 +86,9 @@ def test_embed_ln_and_add_ln(dtype):
     ref = torch.nn.functional.layer_norm(e, (d,), g, b, 1e-12)
     assert (xf - ref).abs().max() < 2e-5
     assert (xa.float() - ref).abs().max() < (2e-5 if dtype == _lib.F32 else 3e-2)
-    y = _rand((M, d), 6)
-    ref2 = torch.nn.functional.layer_norm(y + xf, (d,), g, b, 1e-12)
-    _lib.check(l.itb_add_ln(dtype, _lib.ptr(ctl), _lib.ptr(y), _lib.ptr(g), _lib.ptr(b), 1e-12, _lib.ptr(xf), _lib.ptr(xa),
+    y = _rand((3, M, d), 6)          # three split-K partials of the producing GEMM
+    ref2 = torch.nn.functional.layer_norm(y.sum(0) + xf, (d,), g, b, 1e-12)
+    _lib.check(l.itb_add_ln(dtype, _lib.ptr(ctl), _lib.ptr(y), 3, _lib.ptr(g), _lib.ptr(b), 1e-12, _lib.ptr(xf), _lib.ptr(xa),
                             M, d, stream()))
     torch.cuda.synchronize()
     assert (xf - ref2).abs().max() < 2e-5
