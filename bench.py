@@ -35,7 +35,8 @@ def parse():
     ap.add_argument("--batch", type=int, default=4000)
     ap.add_argument("--capacity", type=int, default=600)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp16", "fp32"])
-    ap.add_argument("--lanes", type=int, default=4, help="batches in flight per GPU (separate streams; results do not depend on it)")
+    ap.add_argument("--rows", type=int, default=1024, help="beam rows per super-batch (consecutive reference batches decoded in lockstep)")
+    ap.add_argument("--lanes", type=int, default=2, help="batches in flight per GPU (separate streams; results do not depend on it)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sentences", type=int, default=6)
     return ap.parse_args()
@@ -185,7 +186,7 @@ def run_b200(args, rank, world, local_rank):
     def one_pass(kws, gather):
         outs, n0 = [], gen.kernel_launches
         with torch.no_grad():
-            for o in gen.forward_many(kws, lanes=args.lanes):
+            for o in gen.forward_many(kws, lanes=args.lanes, rows=args.rows):
                 outs += o
         n_launch = gen.kernel_launches - n0
         if gather and world > 1:
@@ -231,7 +232,7 @@ def run_b200(args, rank, world, local_rank):
         "config": {"workload": "configs[1]: MassSeq2Seq base V=60000 6+6 d=768 beam 4, %d synthetic sentences/rank len 16-128 "
                                "length-sorted, --batch %d --capacity %d (%d batches/rank), random-init weights" % (
                                    args.sentences, args.batch, args.capacity, len(batches)),
-                   "beam": BEAM, "lanes": args.lanes, "sentences_per_rank": args.sentences, "batches_per_rank": len(batches),
+                   "beam": BEAM, "lanes": args.lanes, "superbatch_rows": args.rows, "sentences_per_rank": args.sentences, "batches_per_rank": len(batches),
                    "l2": "working set > L2: 191 MB of bf16 weights streamed every search step plus the KV cache",
                    "parallelism": "dp%d (whole batches per rank, one all_gather of outputs at the end)" % world},
         "e2e": {"value": toks_e / (ms_e / 1000.0), "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libitb.so")
 F32, BF16, F16 = 0, 1, 2      # (weights, activations): (f32,f32) / (bf16,bf16) / (fp16,fp16); include/itb.h
 GEMM_AUTO, GEMM_SIMT, GEMM_TCGEN05 = 0, 1, 2
 EPI_BIAS_F32, EPI_BIAS_GELU_ACT, EPI_BIAS_ACT = 0, 1, 2
-ABI_VERSION = 2
+ABI_VERSION = 3
 Y_PARTIALS = 4
 
 P = C.c_void_p
@@ -20,6 +20,10 @@ P = C.c_void_p
 
 class Ctl(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("step", "done", "steps_run", "cur", "fin_rows", "sent_done", "max_len", "pad_")]
+
+
+class Grp(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("done", "steps_run", "max_len", "fin_rows", "n_rows", "final_cur", "pad0_", "pad1_")]
 
 
 class Layer(C.Structure):
@@ -33,7 +37,9 @@ class Config(C.Structure):
                                 "eos_id", "n_chunk", "reserved0")]
         + [("len_alpha", C.c_float), ("ln_eps", C.c_float)]
         + [(n, P) for n in ("emb_word", "emb_pos", "emb_type", "emb_ln_g", "emb_ln_b", "layers_host", "w_vocab",
-                            "b_vocab", "tgt_lang", "max_lens", "src_mask", "cross_kv", "ctl", "tokens", "anc", "scores",
+                            "b_vocab", "tgt_lang", "max_lens", "sent_grp", "mem_len", "grp", "sent_done")]
+        + [("G", C.c_int), ("reserved1", C.c_int)]
+        + [(n, P) for n in ("src_mask", "cross_kv", "ctl", "tokens", "anc", "scores",
                             "sizes", "fin", "kv_self", "x_f32", "x_act", "qkv", "ctx", "y", "ffn_h", "logits",
                             "cand_val", "cand_idx", "chunk_max", "chunk_sum", "sent_counter")])
 
@@ -47,12 +53,12 @@ _SIGS = {
     "itb_linear": (C.c_int, [C.c_int, C.c_int, C.c_int, P, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, P]),
     "itb_embed_ln": (C.c_int, [C.c_int, P, P, P, P, P, P, P, P, C.c_float, P, P, C.c_int, C.c_int, C.c_int, C.c_int, P]),
     "itb_add_ln": (C.c_int, [C.c_int, P, P, C.c_int, P, P, C.c_float, P, P, C.c_int, C.c_int, P]),
-    "itb_self_attention": (C.c_int, [C.c_int, P, P, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, P]),
-    "itb_cross_attention": (C.c_int, [C.c_int, P, P, C.c_int, P, C.c_int, P, P, C.c_int, C.c_int, C.c_int, C.c_int,
+    "itb_self_attention": (C.c_int, [C.c_int, P, P, P, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, P]),
+    "itb_cross_attention": (C.c_int, [C.c_int, P, P, P, P, C.c_int, P, C.c_int, P, P, C.c_int, C.c_int, C.c_int, C.c_int,
                                       C.c_int, C.c_int, P]),
     "itb_beam_step": (C.c_int, [C.POINTER(Config), P]),
-    "itb_finalize": (C.c_int, [P, P, P, C.c_int, P, P, P, C.c_int, C.c_int, C.c_int, P]),
-    "itb_init_state": (C.c_int, [C.POINTER(Config), P, C.c_int, P]),
+    "itb_finalize": (C.c_int, [P, P, P, P, P, C.c_int, P, P, P, C.c_int, C.c_int, C.c_int, P]),
+    "itb_init_state": (C.c_int, [C.POINTER(Config), P, P, P]),
     "itb_decoder_create": (C.c_int, [C.POINTER(Config), C.POINTER(P)]),
     "itb_decoder_destroy": (C.c_int, [P]),
     "itb_decoder_step": (C.c_int, [P, P]),

@@ -165,11 +165,11 @@ int itb_decoder_step(itb_decoder* dec, void* stream) {
         const itb_layer& w = dec->layers[l];
         char* kv_l = reinterpret_cast<char*>(c.kv_self) + (size_t)l * M * c.T_max * 2 * D * esz;
         ITB_TRY(dec->qkv[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(itb_self_attention(c.dtype, c.ctl, c.qkv, kv_l, c.anc, c.ctx, M, c.beam, D, c.H, c.T_max, stream));
+        ITB_TRY(itb_self_attention(c.dtype, c.ctl, c.sent_done, c.qkv, kv_l, c.anc, c.ctx, M, c.beam, D, c.H, c.T_max, stream));
         ITB_TRY(dec->o[l].run(c.dtype, c.ctl, s));
         ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->o[l].nsplit, w.ln1_g, w.ln1_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
         ITB_TRY(dec->cq[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(itb_cross_attention(c.dtype, c.ctl, c.qkv, 3 * D, c.cross_kv, l, c.src_mask, c.ctx, M, c.beam, D, c.H,
+        ITB_TRY(itb_cross_attention(c.dtype, c.ctl, c.sent_done, c.mem_len, c.qkv, 3 * D, c.cross_kv, l, c.src_mask, c.ctx, M, c.beam, D, c.H,
                                     c.S, c.L, stream));
         ITB_TRY(dec->co[l].run(c.dtype, c.ctl, s));
         ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->co[l].nsplit, w.ln2_g, w.ln2_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));

@@ -51,6 +51,8 @@ template <> struct Raw8<__half> {
 
 struct AttnArgs {
     const ItbCtl* ctl;
+    const int* sent_done;                // [B] 1 = the sentence's group has terminated (rows are skipped); may be null
+    const int* mem_len;                  // cross: [B] memory positions of the sentence (<= S); null = S
     const float* q; int ldq;             // f32 queries, row stride ldq (self: the qkv buffer, k at +d, v at +2d)
     void* kv;                            // self: cache of this layer [M][T_max][2][d]; cross: [B][S][L][2][d]
     const unsigned char* anc;            // self: [2][M][T_max]
@@ -67,6 +69,7 @@ __global__ void __launch_bounds__(AT_THREADS) attn_kernel(AttnArgs a) {
     pdl_wait();
     const ItbCtl* ctl = a.ctl;
     if (ctl != nullptr && ctl->done) return;
+    if (a.sent_done != nullptr && a.sent_done[SELF ? blockIdx.x / a.beam : blockIdx.x] != 0) return;
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, g = lane >> 3, j = lane & 7;
     const int h = blockIdx.y, d = a.d;
     int n, row0, nq;
@@ -84,7 +87,7 @@ __global__ void __launch_bounds__(AT_THREADS) attn_kernel(AttnArgs a) {
     } else {
         const int b = blockIdx.x, q0 = blockIdx.z * NQ;
         row0 = b * a.beam + q0; nq = min(NQ, a.beam - q0);
-        n = a.S;
+        n = (a.mem_len != nullptr) ? a.mem_len[b] : a.S;
         kbase = reinterpret_cast<const T*>(a.kv) + ((size_t)b * a.S * a.L + a.layer) * 2 * d + h * DH;
         pos_stride = (size_t)a.L * 2 * d;
     }
@@ -241,12 +244,13 @@ static int launch_cross(const AttnArgs& a, int H, cudaStream_t s) {
 
 extern "C" {
 
-int itb_self_attention(int dtype, const itb_ctl* ctl, const float* qkv, void* kv_layer, const unsigned char* anc,
-                       void* ctx, int M, int beam, int d, int H, int T_max, void* stream) {
+int itb_self_attention(int dtype, const itb_ctl* ctl, const int* sent_done, const float* qkv, void* kv_layer,
+                       const unsigned char* anc, void* ctx, int M, int beam, int d, int H, int T_max, void* stream) {
     ITB_REQUIRE(d == H * DH, "self_attention: head_dim must be 64 (d == 64*H)");
     ITB_REQUIRE(T_max <= 2048, "self_attention: T_max too large for the shared-memory score buffer");
     AttnArgs a = {};
     a.ctl = reinterpret_cast<const ItbCtl*>(ctl);
+    a.sent_done = sent_done;
     a.q = qkv; a.ldq = 3 * d; a.kv = kv_layer; a.anc = anc; a.ctx = ctx;
     a.M = M; a.beam = beam; a.d = d; a.T_max = T_max;
     if (dtype == ITB_BF16) return launch_self<__nv_bfloat16>(a, H, (cudaStream_t)stream);
@@ -254,14 +258,15 @@ int itb_self_attention(int dtype, const itb_ctl* ctl, const float* qkv, void* kv
     return launch_self<float>(a, H, (cudaStream_t)stream);
 }
 
-int itb_cross_attention(int dtype, const itb_ctl* ctl, const float* q, int ldq, const void* cross_kv, int layer,
-                        const unsigned char* src_mask, void* ctx, int M, int beam, int d, int H, int S, int L,
-                        void* stream) {
+int itb_cross_attention(int dtype, const itb_ctl* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
+                        const void* cross_kv, int layer, const unsigned char* src_mask, void* ctx, int M, int beam, int d,
+                        int H, int S, int L, void* stream) {
     ITB_REQUIRE(d == H * DH, "cross_attention: head_dim must be 64 (d == 64*H)");
     ITB_REQUIRE(S <= 2048, "cross_attention: S too large for the shared-memory score buffer");
     ITB_REQUIRE(M % beam == 0, "cross_attention: M must be a multiple of the beam width");
     AttnArgs a = {};
     a.ctl = reinterpret_cast<const ItbCtl*>(ctl);
+    a.sent_done = sent_done; a.mem_len = mem_len;
     a.q = q; a.ldq = ldq; a.kv = const_cast<void*>(cross_kv); a.mask = src_mask; a.ctx = ctx;
     a.M = M; a.beam = beam; a.d = d; a.S = S; a.L = L; a.layer = layer;
     if (dtype == ITB_BF16) return launch_cross<__nv_bfloat16>(a, H, (cudaStream_t)stream);

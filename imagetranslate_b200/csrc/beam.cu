@@ -17,6 +17,7 @@
 
 struct BeamArgs {
     ItbCtl* ctl;
+    ItbGrp* grp; const int* sent_grp; int* sent_done; int G;
     const float* logits; int ldl;
     int B, beam, V, T_max, n_chunk, chunk, pad_id, eos_id;
     float alpha;
@@ -75,9 +76,11 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     const int c = blockIdx.x, r = blockIdx.y, b = r / a.beam, kslot = r % a.beam;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
 
+    const int gid = a.sent_grp[b];
+    const bool gdone = a.sent_done[b] != 0;                                  // this sentence's reference batch has ended
     const bool lim = (!first) && (a.max_lens[b] < step + 1);                 // seq_gen.py:138
     const bool row_zero = (a.fin[(size_t)cur * M + r] != 0) || lim;          // :195-197
-    const bool skip = row_zero || (first && kslot != 0);                     // step 1 has one row per sentence (:146,221)
+    const bool skip = gdone || row_zero || (first && kslot != 0);            // step 1 has one row per sentence (:146,221)
 
     if (!skip) {
         float v[KT]; int id[KT];
@@ -162,6 +165,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     if (!s_last) return;
 
     // ---------------------------------- phase 2 (one CTA per sentence) ----------------------------------
+    if (!gdone) {
     const int nrows = first ? 1 : K;
     float* rc_val = s_val;      // [nrows][K] row candidates (sentence-level values)
     int* rc_idx = s_idx;
@@ -223,7 +227,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
             unsigned char f = (a.fin[(size_t)cur * M + ro] != 0 || word == a.eos_id) ? 1 : 0;
             a.fin[(size_t)nxt * M + rn] = f;
             unsigned nf = __ballot_sync(__activemask(), f != 0);
-            if (lane == 0) atomicAdd(&ctl->fin_rows, __popc(nf));
+            if (lane == 0) atomicAdd(&a.grp[gid].fin_rows, __popc(nf));
         }
     }
     __syncthreads();
@@ -240,21 +244,41 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
         }
         if (tid == 0) tnew[step] = s_word[j];
     }
+    }   // !gdone
     __syncthreads();
     if (tid == 0) {
         a.sent_counter[b] = 0;
         __threadfence();
         int t = atomicAdd(&ctl->sent_done, 1);
-        if (t == a.B - 1) {
-            __threadfence();
-            int total_fin = atomicAdd(&ctl->fin_rows, 0);
-            ctl->steps_run = step;
-            ctl->step = step + 1;
-            ctl->cur = nxt;
-            ctl->fin_rows = 0;
-            ctl->sent_done = 0;
-            ctl->done = (total_fin == M || step + 1 >= ctl->max_len) ? 1 : 0;                // :131,134
+        s_last = (t == a.B - 1);
+        if (s_last) __threadfence();
+    }
+    __syncthreads();
+    if (!s_last) return;
+    // ---- the last sentence of the step: per-group termination (seq_gen.py:131,134), then advance the step ----
+    __shared__ int s_all_done;
+    if (tid == 0) s_all_done = 1;
+    __syncthreads();
+    for (int g = tid; g < a.G; g += blockDim.x) {
+        ItbGrp* gp = a.grp + g;
+        if (gp->done == 0) {
+            const int fin_rows = atomicAdd(&gp->fin_rows, 0);
+            gp->steps_run = step;
+            gp->fin_rows = 0;
+            if (fin_rows == gp->n_rows || step + 1 >= gp->max_len) { gp->done = 1; gp->final_cur = nxt; }
+            else atomicAnd(&s_all_done, 0);
         }
+    }
+    __syncthreads();
+    for (int i = tid; i < a.B; i += blockDim.x)
+        if (a.sent_done[i] == 0 && a.grp[a.sent_grp[i]].done != 0) a.sent_done[i] = 1;
+    __syncthreads();
+    if (tid == 0) {
+        ctl->steps_run = step;
+        ctl->step = step + 1;
+        ctl->cur = nxt;
+        ctl->sent_done = 0;
+        ctl->done = s_all_done;
     }
 }
 
@@ -270,6 +294,8 @@ int itb_beam_step(const itb_config* c, void* stream) {
     ITB_REQUIRE(c->n_chunk >= 1 && c->n_chunk <= 32, "beam_step: n_chunk must be in [1,32]");
     BeamArgs a;
     a.ctl = reinterpret_cast<ItbCtl*>(c->ctl);
+    a.grp = reinterpret_cast<ItbGrp*>(c->grp); a.sent_grp = c->sent_grp; a.sent_done = c->sent_done; a.G = c->G;
+    ITB_REQUIRE(a.grp != nullptr && a.sent_grp != nullptr && a.sent_done != nullptr && a.G >= 1, "beam_step: group arrays missing");
     a.logits = c->logits; a.ldl = (c->V + 3) / 4 * 4;
     a.B = c->B; a.beam = c->beam; a.V = c->V; a.T_max = c->T_max; a.n_chunk = c->n_chunk;
     a.chunk = (((c->V + c->n_chunk - 1) / c->n_chunk) + 3) / 4 * 4;

@@ -27,6 +27,17 @@ struct ItbCtl {
 // depend on earlier kernels (barrier / TMEM set-up, weight-tile TMA loads), and calls pdl_wait() before touching
 // anything an earlier kernel wrote (or writing anything an earlier kernel reads).  pdl_wait() returns once the
 // predecessor grid has completed and flushed; pdl_trigger() lets the successor be scheduled.
+// Per-group (= per reference batch) control block of a super-batch; mirrors itb_grp in include/itb.h.
+struct ItbGrp {
+    int done;        // the group's loop has ended (every row holds EOS before a step, or step reached max_len)
+    int steps_run;   // steps executed for this group
+    int max_len;     // loop bound of seq_gen.py:131 for this group
+    int fin_rows;    // accumulator: rows of the group whose NEW prefix holds an EOS
+    int n_rows;      // rows (sentences * beam) of the group
+    int final_cur;   // ping-pong parity holding the group's final state
+    int pad0_, pad1_;
+};
+
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 

@@ -84,9 +84,10 @@ __global__ void __launch_bounds__(256) add_ln_kernel(const ItbCtl* __restrict__ 
 }
 
 // seq_gen.py:109-123: prefix = first token in every slot, scores 0, sizes 0; ancestors = own slot.
-__global__ void init_state_kernel(ItbCtl* ctl, int* tokens, unsigned char* anc, float* scores, float* sizes,
-                                  unsigned char* fin, int* sent_counter, const int* __restrict__ first_tokens, int B,
-                                  int beam, int T_max, int eos, int max_len) {
+__global__ void init_state_kernel(ItbCtl* ctl, ItbGrp* grp, int* sent_done, const int* __restrict__ sent_grp,
+                                  const int* __restrict__ grp_max_len, int G, int* tokens, unsigned char* anc,
+                                  float* scores, float* sizes, unsigned char* fin, int* sent_counter,
+                                  const int* __restrict__ first_tokens, int B, int beam, int T_max, int eos) {
     const int M = B * beam;
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
     const int n = gridDim.x * blockDim.x;
@@ -96,34 +97,55 @@ __global__ void init_state_kernel(ItbCtl* ctl, int* tokens, unsigned char* anc, 
         tokens[i] = (p == 0) ? first_tokens[r / beam] : 0;
         anc[i] = (unsigned char)(r % beam);
     }
-    int fin_rows = 0;
     for (int i = tid; i < 2 * M; i += n) {
         scores[i] = 0.f;
         sizes[i] = 0.f;
         fin[i] = (first_tokens[(i % M) / beam] == eos) ? 1 : 0;
     }
     for (int i = tid; i < B; i += n) sent_counter[i] = 0;
-    if (tid == 0) {
-        for (int r = 0; r < M; ++r) fin_rows += (first_tokens[r / beam] == eos) ? 1 : 0;
-        ctl->step = 1;
-        ctl->steps_run = 0;
-        ctl->cur = 0;
-        ctl->fin_rows = 0;                           // accumulator of the NEXT state's EOS rows (beam kernel)
-        ctl->sent_done = 0;
-        ctl->max_len = max_len;
-        // seq_gen.py:131-136: loop body runs for i in [1, max_len) unless every row already holds EOS
-        ctl->done = (max_len <= 1 || fin_rows == M) ? 1 : 0;
+    if (blockIdx.x == 0) {
+        // group bookkeeping by one CTA (G and B are small)
+        __shared__ int all_done;
+        if (threadIdx.x == 0) all_done = 1;
+        __syncthreads();
+        for (int g = threadIdx.x; g < G; g += blockDim.x) {
+            int rows = 0, fin_rows = 0;
+            for (int b = 0; b < B; ++b)
+                if (sent_grp[b] == g) { rows += beam; fin_rows += (first_tokens[b] == eos) ? beam : 0; }
+            const int ml = grp_max_len[g];
+            // seq_gen.py:131-136: loop body runs for i in [1, max_len) unless every row already holds EOS
+            const int done = (ml <= 1 || fin_rows == rows) ? 1 : 0;
+            grp[g].done = done; grp[g].steps_run = 0; grp[g].max_len = ml; grp[g].fin_rows = 0;
+            grp[g].n_rows = rows; grp[g].final_cur = 0; grp[g].pad0_ = 0; grp[g].pad1_ = 0;
+            if (!done) atomicAnd(&all_done, 0);
+        }
+        __syncthreads();
+        for (int b = threadIdx.x; b < B; b += blockDim.x) sent_done[b] = grp[sent_grp[b]].done;
+        if (threadIdx.x == 0) {
+            int ml = 0;
+            for (int g = 0; g < G; ++g) ml = max(ml, grp_max_len[g]);
+            ctl->step = 1;
+            ctl->steps_run = 0;
+            ctl->cur = 0;
+            ctl->fin_rows = 0;
+            ctl->sent_done = 0;
+            ctl->max_len = ml;
+            ctl->done = all_done;
+        }
     }
 }
 
 // seq_gen.py:229-231 + :6-24 : slot 0, cut before first EOS else at max_lens (clamped to the row length).
-__global__ void finalize_kernel(const ItbCtl* __restrict__ ctl, const int* __restrict__ tokens,
+__global__ void finalize_kernel(const ItbCtl* __restrict__ ctl, const ItbGrp* __restrict__ grp,
+                                const int* __restrict__ sent_grp, const int* __restrict__ tokens,
                                 const int* __restrict__ max_lens, int eos, int* __restrict__ out_tokens,
                                 int* __restrict__ out_len, int* __restrict__ out_len_full, int B, int beam, int T_max) {
     const int b = blockIdx.x;
     const int M = B * beam;
-    const int n_tok = ctl->steps_run + 1;
-    const int* src = tokens + ((size_t)ctl->cur * M + (size_t)b * beam) * T_max;
+    const ItbGrp g = grp[sent_grp[b]];
+    const int n_tok = g.steps_run + 1;
+    const int cur = g.done ? g.final_cur : ctl->cur;
+    const int* src = tokens + ((size_t)cur * M + (size_t)b * beam) * T_max;
     __shared__ int first_eos;
     if (threadIdx.x == 0) first_eos = 0x7fffffff;
     __syncthreads();
@@ -182,18 +204,19 @@ int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, int n_partial, con
     return itb_check_launch("add_ln");
 }
 
-int itb_init_state(const itb_config* c, const int* first_tokens, int max_len, void* stream) {
-    ITB_REQUIRE(max_len <= c->T_max, "init_state: max_len exceeds T_max");
+int itb_init_state(const itb_config* c, const int* first_tokens, const int* grp_max_len, void* stream) {
+    ITB_REQUIRE(c->G >= 1 && c->grp != nullptr && c->sent_grp != nullptr && c->sent_done != nullptr, "init_state: group arrays missing");
     init_state_kernel<<<64, 256, 0, (cudaStream_t)stream>>>(
-        reinterpret_cast<ItbCtl*>(c->ctl), c->tokens, c->anc, c->scores, c->sizes, c->fin, c->sent_counter,
-        first_tokens, c->B, c->beam, c->T_max, c->eos_id, max_len);
+        reinterpret_cast<ItbCtl*>(c->ctl), reinterpret_cast<ItbGrp*>(c->grp), c->sent_done, c->sent_grp, grp_max_len, c->G,
+        c->tokens, c->anc, c->scores, c->sizes, c->fin, c->sent_counter, first_tokens, c->B, c->beam, c->T_max, c->eos_id);
     return itb_check_launch("init_state");
 }
 
-int itb_finalize(const itb_ctl* ctl, const int* tokens, const int* max_lens, int eos, int* out_tokens, int* out_len,
-                 int* out_len_full, int B, int beam, int T_max, void* stream) {
-    finalize_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(reinterpret_cast<const ItbCtl*>(ctl), tokens, max_lens, eos,
-                                                         out_tokens, out_len, out_len_full, B, beam, T_max);
+int itb_finalize(const itb_ctl* ctl, const itb_grp* grp, const int* sent_grp, const int* tokens, const int* max_lens,
+                 int eos, int* out_tokens, int* out_len, int* out_len_full, int B, int beam, int T_max, void* stream) {
+    finalize_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(reinterpret_cast<const ItbCtl*>(ctl),
+                                                         reinterpret_cast<const ItbGrp*>(grp), sent_grp, tokens, max_lens,
+                                                         eos, out_tokens, out_len, out_len_full, B, beam, T_max);
     return itb_check_launch("finalize");
 }
 

@@ -157,7 +157,7 @@ class DecodeEngine(object):
             self._decoders[key] = dec
         return dec
 
-    def _config(self, pw, B, beam, S, T_max, pad, eos, alpha):
+    def _config(self, pw, B, beam, S, T_max, pad, eos, alpha, G=1):
         ws, act, M = self.ws, _ACT[self.dtype_code], B * beam
         V4 = (pw.V + 3) // 4 * 4
         n_chunk = max(1, min(32, -(-2368 // M), pw.V // 1024 if pw.V >= 1024 else 1))
@@ -165,7 +165,7 @@ class DecodeEngine(object):
         c = _lib.Config()
         c.dtype, c.gemm_impl = self.dtype_code, self.gemm_impl
         c.B, c.beam, c.d, c.H, c.F, c.L, c.V, c.S, c.T_max = B, beam, pw.d, pw.H, pw.F, pw.L, pw.V, S, T_max
-        c.pad_id, c.eos_id, c.n_chunk = pad, eos, n_chunk
+        c.pad_id, c.eos_id, c.n_chunk, c.G = pad, eos, n_chunk, G
         c.len_alpha, c.ln_eps = alpha, pw.ln_eps
         c.emb_word, c.emb_pos, c.emb_type = pw.emb_word.data_ptr(), pw.emb_pos.data_ptr(), pw.emb_type.data_ptr()
         c.emb_ln_g, c.emb_ln_b = pw.emb_ln_g.data_ptr(), pw.emb_ln_b.data_ptr()
@@ -174,6 +174,8 @@ class DecodeEngine(object):
         i32, u8, f32 = torch.int32, torch.uint8, torch.float32
         t = dict(
             tgt_lang=ws.get("tgt_lang", B, i32), max_lens=ws.get("max_lens", B, i32),
+            sent_grp=ws.get("sent_grp", B, i32), mem_len=ws.get("mem_len", B, i32), grp=ws.get("grp", 8 * G, i32),
+            sent_done=ws.get("sent_done", B, i32),
             src_mask=ws.get("src_mask", B * S, u8), cross_kv=ws.get("cross_kv", B * S * pw.L * 2 * pw.d, act),
             ctl=ws.get("ctl", 8, i32), tokens=ws.get("tokens", 2 * M * T_max, i32), anc=ws.get("anc", 2 * M * T_max, u8),
             scores=ws.get("scores", 2 * M, f32), sizes=ws.get("sizes", 2 * M, f32), fin=ws.get("fin", 2 * M, u8),
@@ -186,31 +188,66 @@ class DecodeEngine(object):
         for k, v in t.items():
             setattr(c, k, v.data_ptr())
         t["out_tok"], t["out_len"] = ws.get("out_tok", B * T_max, i32), ws.get("out_len", 2 * B + 8, i32)
+        t["first"], t["grp_max_len"] = ws.get("first", B, i32), ws.get("grp_max_len", G, i32)
+        t["memory"] = ws.get("memory", B * S * pw.d, act)
         return c, t
 
     @torch.no_grad()
     def decode(self, pw, memory, src_mask, first_tokens, tgt_type_ids, max_lens, max_len, beam, pad, eos, alpha, trace=None):
-        """memory (B,S,d) on device; src_mask (B,S) bool or None; first_tokens/tgt_type_ids/max_lens (B,) ints.
-        Returns (tokens (B,T_max) int32 CPU, lengths (B,), full_lengths (B,))."""
+        """One reference batch.  memory (B,S,d) on device; src_mask (B,S) bool or None; first_tokens/tgt_type_ids/
+        max_lens (B,) ints.  Returns (tokens (B,T_max) int32 CPU, lengths (B,), full_lengths (B,))."""
+        return self.decode_groups(pw, [dict(memory=memory, src_mask=src_mask, first_tokens=first_tokens,
+                                            tgt_type_ids=tgt_type_ids, max_lens=max_lens, max_len=max_len)],
+                                  beam, pad, eos, alpha, trace)[0]
+
+    @torch.no_grad()
+    def decode_groups(self, pw, groups, beam, pad, eos, alpha, trace=None):
+        """Decodes several reference batches ("groups") in lockstep as ONE super-batch: their rows share every kernel
+        launch and every weight byte streamed per step, while each group keeps its own loop bound, termination rule and
+        memory length, so each group's result is exactly what decoding it alone gives.  groups: list of dicts with the
+        arguments of `decode`.  Returns a list of (tokens (B_g,T_max) int32 CPU, lengths, full_lengths)."""
         lib, dev = self.lib, self.device
-        B, S, d = memory.shape
+        G = len(groups)
+        Bs = [int(g["memory"].shape[0]) for g in groups]
+        Ss = [int(g["memory"].shape[1]) for g in groups]
+        B, S, d = sum(Bs), max(Ss), int(groups[0]["memory"].shape[2])
         if d != pw.d:
             raise RuntimeError("memory width %d does not match the decoder width %d" % (d, pw.d))
-        T_max = max(int(max_len), 2)
-        cfg, t = self._config(pw, B, beam, S, T_max, pad, eos, alpha)
+        max_len = max(int(g["max_len"]) for g in groups)
+        T_max = max(max_len, 2)
+        has_mask = any(g["src_mask"] is not None for g in groups)
+        cfg, t = self._config(pw, B, beam, S, T_max, pad, eos, alpha, G)
         stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-        t["tgt_lang"][:B].copy_(tgt_type_ids.to(device=dev, dtype=torch.int32), non_blocking=True)
-        t["max_lens"][:B].copy_(max_lens.to(device=dev, dtype=torch.int32), non_blocking=True)
-        if src_mask is not None:
-            t["src_mask"][:B * S].copy_(src_mask.to(device=dev).reshape(-1).to(torch.uint8), non_blocking=True)
-        else:
+        i32 = torch.int32
+        cat = lambda k: torch.cat([g[k].to(device=dev, dtype=i32, non_blocking=True).reshape(-1) for g in groups])
+        t["tgt_lang"][:B].copy_(cat("tgt_type_ids"), non_blocking=True)
+        t["max_lens"][:B].copy_(cat("max_lens"), non_blocking=True)
+        t["first"][:B].copy_(cat("first_tokens"), non_blocking=True)
+        meta = torch.tensor([gi for gi, n in enumerate(Bs) for _ in range(n)] + [Ss[gi] for gi, n in enumerate(Bs) for _ in range(n)]
+                            + [int(g["max_len"]) for g in groups], dtype=i32).pin_memory().to(dev, non_blocking=True)
+        t["sent_grp"][:B].copy_(meta[:B], non_blocking=True)
+        t["mem_len"][:B].copy_(meta[B:2 * B], non_blocking=True)
+        t["grp_max_len"][:G].copy_(meta[2 * B:], non_blocking=True)
+        mem_all = t["memory"][:B * S * d].view(B, S, d)
+        mask_all = t["src_mask"][:B * S].view(B, S)
+        if G > 1:
+            mem_all.zero_()
+        o = 0
+        for g, Bg, Sg in zip(groups, Bs, Ss):
+            mem_all[o:o + Bg, :Sg].copy_(g["memory"], non_blocking=True)
+            if has_mask:
+                if g["src_mask"] is not None:
+                    mask_all[o:o + Bg, :Sg].copy_(g["src_mask"].to(device=dev), non_blocking=True)
+                else:
+                    mask_all[o:o + Bg, :Sg].fill_(1)
+            o += Bg
+        if not has_mask:
             cfg.src_mask = None
-        first = first_tokens.to(device=dev, dtype=torch.int32).contiguous()
-        mem = memory.to(dtype=_ACT[self.dtype_code]).contiguous()
-        _lib.check(lib.itb_cross_kv(self.dtype_code, self.gemm_impl, _lib.ptr(mem), _lib.ptr(pw.w_ckv), _lib.ptr(pw.b_ckv),
+        _lib.check(lib.itb_cross_kv(self.dtype_code, self.gemm_impl, _lib.ptr(mem_all), _lib.ptr(pw.w_ckv), _lib.ptr(pw.b_ckv),
                                     _lib.ptr(t["cross_kv"]), B * S, pw.d, pw.L, stream), "cross_kv")
-        _lib.check(lib.itb_init_state(C.byref(cfg), _lib.ptr(first), int(max_len), stream), "init_state")
-        key = (pw.uid, B, beam, S, T_max, src_mask is not None, pad, eos, float(alpha))
+        _lib.check(lib.itb_init_state(C.byref(cfg), _lib.ptr(t["first"]), _lib.ptr(t["grp_max_len"]), stream), "init_state")
+        src_mask = True if has_mask else None
+        key = (pw.uid, B, beam, S, T_max, has_mask, pad, eos, float(alpha), G)
         dec = self._decoder(key, cfg)
         n_steps = max(int(max_len) - 1, 0)
         if trace is None and self.use_graph and n_steps > 0:
@@ -254,7 +291,8 @@ class DecodeEngine(object):
                 if i % self.poll_every == 0 and i < n_steps and int(t["ctl"][1].item()) != 0:   # ctl.done
                     break
         out_tok, out_len = t["out_tok"], t["out_len"]
-        _lib.check(lib.itb_finalize(_lib.ptr(t["ctl"]), _lib.ptr(t["tokens"]), _lib.ptr(t["max_lens"]), eos,
+        _lib.check(lib.itb_finalize(_lib.ptr(t["ctl"]), _lib.ptr(t["grp"]), _lib.ptr(t["sent_grp"]), _lib.ptr(t["tokens"]),
+                                    _lib.ptr(t["max_lens"]), eos,
                                     _lib.ptr(out_tok), _lib.ptr(out_len), C.c_void_p(out_len.data_ptr() + 4 * B),
                                     B, beam, T_max, stream), "finalize")
         tok = out_tok[:B * T_max].view(B, T_max).cpu()
@@ -262,4 +300,8 @@ class DecodeEngine(object):
         lens = out_len[:2 * B + 8].cpu()
         self.last_steps = int(lens[2 * B + 2])
         self.launches_per_step = 2 + 11 * pw.L
-        return tok, lens[:B], lens[B:2 * B]
+        res, o = [], 0
+        for Bg in Bs:
+            res.append((tok[o:o + Bg], lens[o:o + Bg], lens[B + o:B + o + Bg]))
+            o += Bg
+        return res

@@ -88,9 +88,11 @@ class BeamDecoder(nn.Module):
         self._packed.clear()
 
     # ------------------------------------------------------------------ forward
-    def forward(self, src_inputs=None, src_sizes=None, first_tokens=None, src_mask=None, src_langs=None, tgt_langs=None,
-                pad_idx=None, max_len: int = None, unpad_output: bool = True, beam_width: int = None, images=None,
-                proposals=None, image_embed=None):
+    def _prepare(self, src_inputs=None, src_sizes=None, first_tokens=None, src_mask=None, src_langs=None, tgt_langs=None,
+                 pad_idx=None, max_len: int = None, unpad_output: bool = True, beam_width: int = None, images=None,
+                 proposals=None, image_embed=None):
+        """Everything of reference src/seq_gen.py:57-129 that happens before the search loop: argument unwrapping,
+        the encoder call, max_len / max_lens.  Returns one decode "group" (= this reference batch)."""
         if isinstance(tgt_langs, list):                       # :57-72
             assert len(tgt_langs) == 1
             tgt_langs = tgt_langs[0]
@@ -144,49 +146,105 @@ class BeamDecoder(nn.Module):
         if src_inputs is None:
             max_lens = torch.full((B,), int(max_len), dtype=torch.int64)
         else:
-            max_lens = torch.tensor([mlf(int(x)) for x in src_sizes], dtype=torch.int64)   # :121
+            # :121 -- same IEEE double arithmetic as python's int(a * s + b), on whatever device src_sizes lives
+            max_lens = (src_sizes.to(torch.float64) * self.max_len_a + self.max_len_b).to(torch.int64).clamp(max=n_pos)
         max_len = min(int(max_len), n_pos)
-
         code = self._dtype_code(wemb)
-        eng = self._engine(device, code)
-        pw = self._weights(model, batch_lang, code, device)
-        tok, lens, lens_full = eng.decode(pw, memory, mem_mask, first_tokens, tgt_langs, max_lens, max_len, beam_width,
-                                          int(pad_idx), int(eos), float(self.len_penalty_ratio))
+        return dict(memory=memory, src_mask=mem_mask, first_tokens=first_tokens, tgt_type_ids=tgt_langs, max_lens=max_lens,
+                    max_len=max_len, B=B, beam=int(beam_width), pad=int(pad_idx), eos=int(eos), unpad=bool(unpad_output),
+                    lang=batch_lang, code=code, device=device, model=model)
+
+    def _decode_groups(self, groups):
+        """Runs one super-batch (groups sharing decoder weights / beam / pad / eos) and returns the reference's output
+        lists (src/seq_gen.py:229-242), one per group."""
+        g0 = groups[0]
+        eng = self._engine(g0["device"], g0["code"])
+        pw = self._weights(g0["model"], g0["lang"], g0["code"], g0["device"])
+        res = eng.decode_groups(pw, groups, g0["beam"], g0["pad"], g0["eos"], float(self.len_penalty_ratio))
         with self._lock:
             self.kernel_launches += eng.last_steps * eng.launches_per_step + 4
-        tok = tok.to(torch.int64)
-        sel = lens if unpad_output else lens_full
-        return [tok[r, :int(sel[r])].clone() for r in range(B)]
+        outs = []
+        for g, (tok, lens, lens_full) in zip(groups, res):
+            tok = tok.to(torch.int64)
+            sel = (lens if g["unpad"] else lens_full).tolist()
+            outs.append([tok[r, :sel[r]].clone() for r in range(g["B"])])
+        return outs
+
+    def forward(self, src_inputs=None, src_sizes=None, first_tokens=None, src_mask=None, src_langs=None, tgt_langs=None,
+                pad_idx=None, max_len: int = None, unpad_output: bool = True, beam_width: int = None, images=None,
+                proposals=None, image_embed=None):
+        g = self._prepare(src_inputs, src_sizes, first_tokens, src_mask, src_langs, tgt_langs, pad_idx, max_len, unpad_output,
+                          beam_width, images, proposals, image_embed)
+        return self._decode_groups([g])[0]
 
     # ------------------------------------------------------------------ several batches in flight
-    def forward_many(self, batches, lanes: int = 4):
+    @staticmethod
+    def _unwrap(v):
+        return v[0] if isinstance(v, list) else v
+
+    def _pack(self, batches, rows):
+        """Consecutive batches that can share a super-batch (same target-language decoder, beam, pad id, memory kind,
+        similar memory length), up to `rows` beam rows.  Returns a list of index lists."""
+        packs, cur, cur_key, cur_rows, s_lo, s_hi = [], [], None, 0, 0, 0
+        for i, kw in enumerate(batches):
+            first, tl = self._unwrap(kw.get("first_tokens")), self._unwrap(kw.get("tgt_langs"))
+            beam = kw.get("beam_width") or self.beam_width
+            src = self._unwrap(kw.get("src_inputs"))
+            S = int(src.size(1)) if src is not None else 49
+            key = (int(tl[0]), beam, kw.get("pad_idx"), src is None, kw.get("max_len"))
+            n = int(first.numel()) * beam
+            ok = cur and key == cur_key and cur_rows + n <= rows and max(s_hi, S) <= 1.5 * min(s_lo, S)
+            if not ok:
+                if cur:
+                    packs.append(cur)
+                cur, cur_key, cur_rows, s_lo, s_hi = [], key, 0, S, S
+            cur.append(i)
+            cur_rows += n
+            s_lo, s_hi = min(s_lo, S), max(s_hi, S)
+        if cur:
+            packs.append(cur)
+        return packs
+
+    def forward_many(self, batches, lanes: int = 2, rows: int = 1024):
         """Decodes a list of batches (each a dict of `forward` keyword arguments) and returns their outputs in order.
 
-        Every batch is decoded exactly as `forward` would (whole reference batches, never re-batched, so results do
-        not depend on `lanes`), but up to `lanes` batches are in flight on separate CUDA streams, each with its own
-        workspace / KV cache / captured step graph.  A single search step at the reference batch sizes is a chain of
-        ~70 short latency-bound kernels that leaves most SMs idle; independent batches fill them.  This replaces the
-        reference's one-thread-per-GPU `DataParallelModel` fan-out (src/parallel.py:70-148) on ONE device."""
+        Every batch is decoded exactly as `forward` would decode it (same loop bound, termination rule and arithmetic
+        per reference batch, so results do not depend on `lanes` / `rows`), but
+          * consecutive compatible batches are decoded in lockstep as one SUPER-BATCH of up to `rows` beam rows: one
+            kernel chain and one pass over the 191 MB of decoder + vocabulary weights per step serves all of them
+            (a single reference batch at --batch 4000 has 120-940 rows and leaves the step latency-bound);
+          * up to `lanes` super-batches are in flight on separate CUDA streams, each with its own workspace / KV cache /
+            captured step graph, which fills the SMs the dependent-kernel chain of one super-batch leaves idle.
+        This replaces the reference's thread-per-GPU `DataParallelModel` fan-out (src/parallel.py:70-148) on ONE device."""
         batches = list(batches)
-        if lanes <= 1 or len(batches) <= 1:
-            return [self.forward(**kw) for kw in batches]
+        if not batches:
+            return []
         model = self.seq2seq_model.module if hasattr(self.seq2seq_model, "module") else self.seq2seq_model
-        device = model.encoder.embeddings.word_embeddings.weight.device
+        wemb = model.encoder.embeddings.word_embeddings.weight
+        device = wemb.device
         if device.type != "cuda":
             raise RuntimeError("imagetranslate_b200.BeamDecoder needs the model on a CUDA device (no CPU fallback)")
-        lanes = min(lanes, len(batches))
+        packs = self._pack(batches, max(int(rows), 1))
+        results = [None] * len(batches)
+
+        def run_pack(idxs):
+            groups = [self._prepare(**batches[i]) for i in idxs]
+            for i, o in zip(idxs, self._decode_groups(groups)):
+                results[i] = o
+
+        lanes = max(1, min(int(lanes), len(packs)))
+        if lanes == 1:
+            for idxs in packs:
+                run_pack(idxs)
+            return results
         if not hasattr(self, "_streams") or len(self._streams) < lanes:
             self._streams = [torch.cuda.Stream(device=device) for _ in range(lanes)]
             self._pool = ThreadPoolExecutor(max_workers=lanes)
-        # pack the weights once, on the calling thread, before the lanes start
-        wemb = model.encoder.embeddings.word_embeddings.weight
         code = self._dtype_code(wemb)
-        for kw in batches:
-            tl = kw["tgt_langs"][0] if isinstance(kw["tgt_langs"], list) else kw["tgt_langs"]
-            self._weights(model, int(tl[0]), code, device)
+        for kw in batches:                     # pack the weights once, on the calling thread, before the lanes start
+            self._weights(model, int(self._unwrap(kw["tgt_langs"])[0]), code, device)
         ready = torch.cuda.Event()
         ready.record(torch.cuda.current_stream(device))
-        results = [None] * len(batches)
         nxt = [0]
 
         def lane_main(idx):
@@ -198,14 +256,20 @@ class BeamDecoder(nn.Module):
                     with self._lock:
                         i = nxt[0]
                         nxt[0] += 1
-                    if i >= len(batches):
+                    if i >= len(packs):
                         break
-                    results[i] = self.forward(**batches[i])
+                    run_pack(packs[i])
                 done = torch.cuda.Event()
                 done.record(stream)
             return done
 
         futs = [self._pool.submit(lane_main, i) for i in range(lanes)]
+        err = None
         for f in futs:
-            torch.cuda.current_stream(device).wait_event(f.result())     # re-raises a lane's RuntimeError
+            try:
+                torch.cuda.current_stream(device).wait_event(f.result())
+            except Exception as e:             # a lane's RuntimeError surfaces after all lanes stopped
+                err = err or e
+        if err is not None:
+            raise err
         return results

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define ITB_ABI_VERSION 2
+#define ITB_ABI_VERSION 3
 #define ITB_Y_PARTIALS 4   /* cfg.y holds up to this many split-K partial outputs: [ITB_Y_PARTIALS][M][d] floats */
 /* dtype codes: (linear-weight type, activation / KV-cache type).  Accumulation, softmax, LayerNorm statistics,
  * logits and beam scores are always fp32. */
@@ -36,6 +36,10 @@ enum { ITB_EPI_BIAS_F32 = 0,      /* out f32  = acc + bias                      
 
 /* Control block living in device memory (see csrc/common.cuh for field meaning). */
 typedef struct { int step, done, steps_run, cur, fin_rows, sent_done, max_len, pad_; } itb_ctl;
+/* One GROUP = one reference batch (one BeamDecoder.forward call of the reference).  Several groups may be decoded
+ * in lockstep as one super-batch: rows of all groups share every kernel launch (and every weight byte streamed), but
+ * each group keeps the reference's per-batch loop bound and termination rule (seq_gen.py:113-117,131-136). */
+typedef struct { int done, steps_run, max_len, fin_rows, n_rows, final_cur, pad0_, pad1_; } itb_grp;
 
 /* One decoder layer of HF-2.9.0 BertLayer(is_decoder=True). */
 typedef struct {
@@ -63,6 +67,11 @@ typedef struct {
   /* per-call inputs */
   const int* tgt_lang;                      /* [B] token-type id of the target language (seq_gen.py:148)  */
   const int* max_lens;                      /* [B] (seq_gen.py:119-121)                                    */
+  const int* sent_grp;                      /* [B] group (reference batch) of each sentence                */
+  const int* mem_len;                       /* [B] memory positions of the sentence's group (<= S)         */
+  itb_grp* grp;                             /* [G] per-group control blocks                                */
+  int* sent_done;                           /* [B] 1 once the sentence's group has terminated              */
+  int G, reserved1;
   const unsigned char* src_mask;            /* [B][S] 1 = attend, or NULL (image memory, seq_gen.py:153)   */
   const void* cross_kv;                     /* act [B][S][L][2][d]: cross K,V of every layer                */
   /* search state */
@@ -115,14 +124,14 @@ int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, int n_partial, con
 
 /* Single-query causal self-attention over the KV cache through the ancestor table; appends the
  * row's new K,V at position step-1.  HF BertSelfAttention (A.3) on the last position only. */
-int itb_self_attention(int dtype, const itb_ctl* ctl, const float* qkv, void* kv_layer, const unsigned char* anc,
-                       void* ctx, int M, int beam, int d, int H, int T_max, void* stream);
+int itb_self_attention(int dtype, const itb_ctl* ctl, const int* sent_done, const float* qkv, void* kv_layer,
+                       const unsigned char* anc, void* ctx, int M, int beam, int d, int H, int T_max, void* stream);
 
 /* Single-query cross-attention over the per-sentence memory K,V with the additive -10000 source mask
  * (reference src/bert_seq2seq.py:25-38). q has row stride ldq. */
-int itb_cross_attention(int dtype, const itb_ctl* ctl, const float* q, int ldq, const void* cross_kv, int layer,
-                        const unsigned char* src_mask, void* ctx, int M, int beam, int d, int H, int S, int L,
-                        void* stream);
+int itb_cross_attention(int dtype, const itb_ctl* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
+                        const void* cross_kv, int layer, const unsigned char* src_mask, void* ctx, int M, int beam, int d,
+                        int H, int S, int L, void* stream);
 
 /* Fused log-softmax + finished/over-length row zeroing + score add + length-penalty divide + top-k over
  * beam*V + forced-PAD rewrites + back-pointer / prefix / size / score / ancestor-table update + termination
@@ -131,11 +140,12 @@ int itb_beam_step(const itb_config* cfg_host, void* stream);
 
 /* Writes slot 0 of every sentence: out_tokens[B][T_max] and out_len[B] (first-EOS cut or max_lens;
  * reference src/seq_gen.py:229-231 and :6-24).  out_len2[B] = number of tokens produced (unpad_output=False). */
-int itb_finalize(const itb_ctl* ctl, const int* tokens, const int* max_lens, int eos, int* out_tokens, int* out_len,
-                 int* out_len_full, int B, int beam, int T_max, void* stream);
+int itb_finalize(const itb_ctl* ctl, const itb_grp* grp, const int* sent_grp, const int* tokens, const int* max_lens,
+                 int eos, int* out_tokens, int* out_len, int* out_len_full, int B, int beam, int T_max, void* stream);
 
-/* Resets ctl and the search state for a new batch (seq_gen.py:109-123). first_tokens: [B]. */
-int itb_init_state(const itb_config* cfg_host, const int* first_tokens, int max_len, void* stream);
+/* Resets ctl, the group blocks and the search state for a new (super-)batch (seq_gen.py:109-123).
+ * first_tokens: [B]; grp_max_len: [G] loop bound of each group (seq_gen.py:113-117), all <= T_max. */
+int itb_init_state(const itb_config* cfg_host, const int* first_tokens, const int* grp_max_len, void* stream);
 
 /* -------- whole decoder step -------- */
 int itb_decoder_create(const itb_config* cfg_host, itb_decoder** out);

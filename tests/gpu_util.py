@@ -50,15 +50,17 @@ class BeamHarness(object):
         self.t = dict(ctl=z(8, i32), tokens=z(2 * M * T_max, i32), anc=z(2 * M * T_max, u8), scores=z(2 * M, f32),
                       sizes=z(2 * M, f32), fin=z(2 * M, u8), logits=z(M * self.V4, f32), cand_val=z(M * n_chunk * KT, f32),
                       cand_idx=z(M * n_chunk * KT, i32), chunk_max=z(M * n_chunk, f32), chunk_sum=z(M * n_chunk, f32),
-                      sent_counter=z(B, i32), max_lens=torch.tensor(max_lens, dtype=i32, device=DEV))
+                      sent_counter=z(B, i32), max_lens=torch.tensor(max_lens, dtype=i32, device=DEV),
+                      sent_grp=torch.zeros(B, dtype=i32, device=DEV), grp=z(8, i32), sent_done=z(B, i32))
         c = _lib.Config()
         c.dtype, c.B, c.beam, c.V, c.T_max, c.S, c.L, c.d, c.H, c.F = _lib.F32, B, beam, V, T_max, 1, 1, 64, 1, 64
-        c.pad_id, c.eos_id, c.n_chunk, c.len_alpha = pad, eos, n_chunk, alpha
+        c.pad_id, c.eos_id, c.n_chunk, c.len_alpha, c.G = pad, eos, n_chunk, alpha, 1
         for k, v in self.t.items():
             setattr(c, k, v.data_ptr())
         self.cfg = c
         first = torch.tensor(first_tokens, dtype=i32, device=DEV)
-        _lib.check(l.itb_init_state(C.byref(c), _lib.ptr(first), max_len, stream()), "init_state")
+        self.grp_max_len = torch.tensor([max_len], dtype=i32, device=DEV)
+        _lib.check(l.itb_init_state(C.byref(c), _lib.ptr(first), _lib.ptr(self.grp_max_len), stream()), "init_state")
         torch.cuda.synchronize()
 
     def ctl(self):

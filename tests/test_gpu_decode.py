@@ -167,22 +167,27 @@ def test_16bit_free_running_token_agreement(mode):
 
 
 @pytest.mark.parametrize("dtype", ["fp32", "bf16"])
-def test_forward_many_lanes_equal_sequential(dtype):
-    """Several batches in flight on separate streams (forward_many) give exactly the outputs of one-by-one forward
-    calls: batches are never merged or re-batched, and every kernel of the step is deterministic."""
-    model, _ = _fresh_case(61, 3000, 2, 8, 4, 2)
+@pytest.mark.parametrize("eos_bias", [0.0, 1.3])
+def test_forward_many_superbatches_and_lanes_equal_sequential(dtype, eos_bias):
+    """forward_many decodes several reference batches in lockstep as one super-batch (per-group loop bound and
+    termination) and keeps several super-batches in flight on separate streams; every batch must come out exactly as a
+    plain forward call gives it.  eos_bias > 0 makes hypotheses finish early, so groups terminate at different steps."""
+    model, _ = _fresh_case(61, 3000, 2, 8, 4, 2, eos_bias)
     model = model.to(DEV)
     batches = []
-    for i, (B, S) in enumerate([(5, 9), (3, 17), (8, 6), (2, 23), (6, 12), (4, 9), (7, 15)]):
+    for i, (B, S) in enumerate([(5, 9), (3, 10), (8, 12), (2, 11), (6, 17), (4, 18), (7, 6), (1, 7)]):
         src, mask, pad_idx = cases.make_text_batch(B, S, 3000, 100 + i)
         batches.append(dict(src_inputs=src, src_mask=mask, src_sizes=pad_idx, src_langs=torch.zeros(B, dtype=torch.long),
                             first_tokens=torch.full((B,), 6), tgt_langs=torch.ones(B, dtype=torch.long), pad_idx=0))
     bd = BeamDecoder(model, beam_width=4, dtype=dtype, **cases.GEN)
+    assert [len(p) for p in bd._pack(batches, 4096)] == [4, 2, 2]
     with torch.no_grad():
         seq = [bd(**kw) for kw in batches]
-        for lanes in (3, 4):
-            par = bd.forward_many(batches, lanes=lanes)
-            assert [[o.tolist() for o in b] for b in par] == [[o.tolist() for o in b] for b in seq]
+        for lanes, rows in ((1, 4096), (3, 64), (2, 4096), (4, 1)):
+            par = bd.forward_many(batches, lanes=lanes, rows=rows)
+            assert [[o.tolist() for o in b] for b in par] == [[o.tolist() for o in b] for b in seq], (lanes, rows)
     if dtype == "fp32":
-        want = R.beam_search(model.cpu(), beam_width=4, **cases.GEN, **batches[1])
-        assert [o.tolist() for o in seq[1]] == [w.tolist() for w in want]
+        cpu = model.cpu()
+        for i in (1, 4):
+            want = R.beam_search(cpu, beam_width=4, **cases.GEN, **batches[i])
+            assert [o.tolist() for o in seq[i]] == [w.tolist() for w in want]

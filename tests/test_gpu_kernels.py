@@ -108,7 +108,7 @@ def test_self_attention_through_ancestor_table(dtype, step):
     ctl = make_ctl(step=step, cur=1)
     ctx = torch.zeros(M, d, device=DEV, dtype=act)
     kv_before = kv.clone()
-    _lib.check(_lib.lib().itb_self_attention(dtype, _lib.ptr(ctl), _lib.ptr(qkv), _lib.ptr(kv), _lib.ptr(anc), _lib.ptr(ctx),
+    _lib.check(_lib.lib().itb_self_attention(dtype, _lib.ptr(ctl), None, _lib.ptr(qkv), _lib.ptr(kv), _lib.ptr(anc), _lib.ptr(ctx),
                                              M, beam, d, H, T, stream()))
     torch.cuda.synchronize()
     q, kn, vn = qkv[:, :d], qkv[:, d:2 * d].to(act), qkv[:, 2 * d:].to(act)
@@ -143,7 +143,7 @@ def test_cross_attention_with_additive_mask(dtype, masked):
         mask[0, 15:] = 0
         mask[2, 3:] = 0
     ctx = torch.zeros(M, d, device=DEV, dtype=act)
-    _lib.check(_lib.lib().itb_cross_attention(dtype, None, _lib.ptr(q), 3 * d, _lib.ptr(ckv), layer,
+    _lib.check(_lib.lib().itb_cross_attention(dtype, None, None, None, _lib.ptr(q), 3 * d, _lib.ptr(ckv), layer,
                                               _lib.ptr(mask) if masked else None, _lib.ptr(ctx), M, beam, d, H, S, L, stream()))
     torch.cuda.synchronize()
     K = ckv[:, :, layer, 0].double().view(B, S, H, 64).repeat_interleave(beam, 0)

@@ -91,13 +91,13 @@ kv = [rnd(M, T, 2, d, dt=ACT) for _ in range(NB)]
 anc = torch.randint(0, beam, (2, M, T), device=DEV).to(torch.uint8)
 ctx = torch.empty(M, d, dtype=ACT, device=DEV)
 esz = kv[0].element_size()
-total += L * bench("self_attn t=%d" % t, lambda i: _lib.check(lib.itb_self_attention(DT, _lib.ptr(ctl), _lib.ptr(qkv), _lib.ptr(kv[i]),
+total += L * bench("self_attn t=%d" % t, lambda i: _lib.check(lib.itb_self_attention(DT, _lib.ptr(ctl), None, _lib.ptr(qkv), _lib.ptr(kv[i]),
                                                                                       _lib.ptr(anc), _lib.ptr(ctx), M, beam, d, H, T, st())),
                    bytes_alg=M * t * 2 * d * esz, nbuf=NB)
 # cross attention
 ckv = rnd(B, S, L, 2, d, dt=ACT)
 mask = torch.ones(B, S, dtype=torch.uint8, device=DEV)
-total += L * bench("cross_attn S=%d" % S, lambda i: _lib.check(lib.itb_cross_attention(DT, _lib.ptr(ctl), _lib.ptr(qkv), 3 * d, _lib.ptr(ckv),
+total += L * bench("cross_attn S=%d" % S, lambda i: _lib.check(lib.itb_cross_attention(DT, _lib.ptr(ctl), None, None, _lib.ptr(qkv), 3 * d, _lib.ptr(ckv),
                                                                                         i % L, _lib.ptr(mask), _lib.ptr(ctx), M, beam, d, H,
                                                                                         S, L, st())),
                    bytes_alg=B * S * 2 * d * esz, nbuf=NB)
