@@ -1,23 +1,47 @@
 // Single-query attention for the incremental decoder step (head_dim fixed at 64 = 768/12,
 // reference src/lm_config.py:8,13; HF BertSelfAttention).
 //
-// One CTA (4 warps) per (row, head) for self-attention and per (sentence, head, group of <=4 beam slots) for
-// cross-attention -- the beam slots of a sentence share the memory K/V, so each K/V byte is fetched once per group.
-// Positions are split over the warps in runs of 16; inside a warp 8 lanes x 16 B cover one 64-wide head row and
-// 4 positions are processed side by side, 4 such loads in flight per lane (64 positions per CTA iteration):
+// One CTA (4 warps) per (sentence, head, group of <=4 beam slots).  The beam slots of a sentence share K/V rows:
+//   * cross-attention: all of the memory K/V, so each K/V byte is fetched once per group of slots;
+//   * self-attention: the slots' hypotheses descend from a common ancestor, so through the ancestor table written
+//     by the beam kernel they address the SAME physical cache rows for every position before their lineages split
+//     (if two slots share the row of position p they share all earlier rows).  Positions [0,c) are therefore read
+//     once for the whole group and only the divergent tail [c,n) per slot -- the K/V traffic of a beam-4 step is
+//     close to that of ONE hypothesis, and a beam reorder never copies K/V.
+// Positions are dealt to the warps in runs of 16; inside a warp 8 lanes x 16 B cover one 64-wide head row, 4 positions
+// side by side, 4 such loads in flight per lane:
 //   phase A  scores  q.k/8 (+ additive -10000 source mask) -> shared memory
 //   phase B  softmax statistics in fp32: exp(x - max) / sum, as torch.softmax
-//   phase C  sum_p e_p * V[p], reduced over lanes, warps, then normalised and stored in the activation type.
-// Self-attention appends the row's new K,V to the cache first and reads the cache through the ancestor table
-// written by the beam kernel, so a beam reorder never copies K/V.  HBM-bound: 2*d*sizeof(T) bytes per
-// (row, position, layer) for self-attention, per (sentence, position, layer) for cross-attention.
+//   phase C  sum_p e_p * V[p], reduced over lanes and warps, normalised, stored in the activation type.
+// Self-attention appends the rows' new K,V to the cache first.  HBM-bound: 2*d*sizeof(T) bytes per (hypothesis
+// lineage, position, layer) for self-attention, per (sentence, position, layer) for cross-attention.
 #include "common.cuh"
 #include "launch.h"
 
 #define DH 64
+#define NQ_MAX 4
 #define AT_WARPS 4
 #define AT_THREADS (AT_WARPS * 32)
-#define NQ_MAX 4
+
+template <typename T> __device__ __forceinline__ void store8(T* p, const float* v);
+template <> __device__ __forceinline__ void store8<float>(float* p, const float* v) {
+    reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+    reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+template <> __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float* v) {
+    uint4 u;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+    *reinterpret_cast<uint4*>(p) = u;
+}
+template <> __device__ __forceinline__ void store8<__half>(__half* p, const float* v) {
+    uint4 u;
+    __half2* h = reinterpret_cast<__half2*>(&u);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[2 * e], v[2 * e + 1]);
+    *reinterpret_cast<uint4*>(p) = u;
+}
 
 template <typename T> struct Raw8;                       // 8 consecutive head dims of one K/V row
 template <> struct Raw8<float> {
@@ -61,83 +85,120 @@ struct AttnArgs {
     int M, beam, d, T_max, S, L, layer;
 };
 
-// NQ query rows share the K/V rows addressed by `kaddr(p)` (V row = K row + d).
+
+
+// NQ = beam slots handled per CTA (4, or 1 for greedy search).  grid = (sentences, heads, ceil(beam / NQ)).
 template <typename T, int NQ, bool SELF>
-__global__ void __launch_bounds__(AT_THREADS) attn_kernel(AttnArgs a) {
-    extern __shared__ float sm[];
+__global__ void __launch_bounds__(AT_THREADS, 6) attn_kernel(AttnArgs a) {
+    extern __shared__ __align__(16) float sm[];
+    __shared__ int s_c;
     pdl_trigger();
     pdl_wait();
-    const ItbCtl* ctl = a.ctl;
-    if (ctl != nullptr && ctl->done) return;
-    if (a.sent_done != nullptr && a.sent_done[SELF ? blockIdx.x / a.beam : blockIdx.x] != 0) return;
+    // one round trip for all control words: {step, done, steps_run, cur} and the sentence's group flag
+    const int b = blockIdx.x;
+    int4 c4 = make_int4(1, 0, 0, 0);
+    if (a.ctl != nullptr) c4 = *reinterpret_cast<const int4*>(a.ctl);
+    const int sdone = (a.sent_done != nullptr) ? a.sent_done[b] : 0;
+    if (c4.y != 0 || sdone != 0) return;
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, g = lane >> 3, j = lane & 7;
-    const int h = blockIdx.y, d = a.d;
-    int n, row0, nq;
+    const int h = blockIdx.y, d = a.d, q0 = blockIdx.z * NQ;
+    const int row0 = b * a.beam + q0, nq = min(NQ, a.beam - q0);
+    const int n = SELF ? c4.x : ((a.mem_len != nullptr) ? a.mem_len[b] : a.S);    // self: positions 0..step-1
+    const int npad = (n + 3) & ~3;
+    float* sc = sm;                                      // [NQ][npad] scores, then exp(score - max)
+    float* pv = sc + NQ * npad;                          // [AT_WARPS][NQ][DH]
+    float* qs = pv + AT_WARPS * NQ * DH;                 // [NQ][DH] pre-scaled queries
+    float* inv = qs + NQ * DH;                           // [NQ]
+    unsigned char* s_anc = reinterpret_cast<unsigned char*>(inv + NQ);     // SELF: [NQ][n] physical beam slot per position
+
+    // second round trip: queries, the rows' new K,V, the ancestor rows -- all loads issued before any store
+    constexpr int QPT = (NQ * DH + AT_THREADS - 1) / AT_THREADS;           // query elements per thread
+    constexpr int APT = (NQ * 2 * DH + AT_THREADS - 1) / AT_THREADS;       // appended K,V elements per thread
+    float qv[QPT], av[APT];
+#pragma unroll
+    for (int x = 0; x < QPT; ++x) {
+        const int i = tid + x * AT_THREADS;
+        const int qi = i / DH, r = row0 + min(qi, nq - 1);
+        qv[x] = (i < NQ * DH) ? a.q[(size_t)r * a.ldq + h * DH + (i % DH)] : 0.f;
+    }
+    int c = n;                                           // positions [0,c) are shared by the nq slots
     const T* kbase;
     size_t pos_stride;
-    const unsigned char* arow = nullptr;
     if (SELF) {
-        const int r = blockIdx.x;
-        row0 = r; nq = 1;
-        const int pc = ctl->step - 1;                    // position of the new token; attends to 0..pc
-        n = pc + 1;
-        kbase = reinterpret_cast<const T*>(a.kv) + h * DH;
+        const int pc = n - 1;
+#pragma unroll
+        for (int x = 0; x < APT; ++x) {
+            const int i = tid + x * AT_THREADS;
+            const int qi = i / (2 * DH), kvsel = (i / DH) & 1, e = i % DH, r = row0 + qi;
+            av[x] = (i < nq * 2 * DH) ? a.q[(size_t)r * a.ldq + (1 + kvsel) * d + h * DH + e] : 0.f;
+        }
+        for (int i = tid; i < NQ * pc; i += AT_THREADS) {
+            const int qi = i / pc, p = i % pc;
+            const unsigned char* arow = a.anc + ((size_t)c4.w * a.M + row0 + min(qi, nq - 1)) * a.T_max;
+            s_anc[qi * n + p] = arow[p];
+        }
+        // append the rows' K,V (rounded to the cache type) at position pc, then treat it like any cached position
+#pragma unroll
+        for (int x = 0; x < APT; ++x) {
+            const int i = tid + x * AT_THREADS;
+            const int qi = i / (2 * DH), kvsel = (i / DH) & 1, e = i % DH, r = row0 + qi;
+            if (i < nq * 2 * DH)
+                reinterpret_cast<T*>(a.kv)[(((size_t)r * a.T_max + pc) * 2 + kvsel) * d + h * DH + e] = from_f32<T>(av[x]);
+        }
+        if (tid < NQ) s_anc[tid * n + pc] = (unsigned char)((q0 + min(tid, nq - 1)) % a.beam);
+        if (tid == 0) s_c = pc;
+    }
+#pragma unroll
+    for (int x = 0; x < QPT; ++x) {
+        const int i = tid + x * AT_THREADS;
+        if (i < NQ * DH) qs[i] = qv[x] * 0.125f;         // pre-scaled by 1/sqrt(64) (exact: power of two)
+    }
+    __syncthreads();
+    if (SELF) {
+        const int pc = n - 1;
+        if (NQ > 1) {
+            int cmin = pc;
+            for (int p = tid; p < pc; p += AT_THREADS) {
+                bool same = true;
+#pragma unroll
+                for (int qi = 1; qi < NQ; ++qi) same = same && (s_anc[qi * n + p] == s_anc[p]);
+                if (!same) { cmin = p; break; }          // p ascending per thread: first mismatch is this thread's minimum
+            }
+            if (cmin < pc) atomicMin(&s_c, cmin);
+            __syncthreads();
+            c = s_c;
+        }
+        kbase = reinterpret_cast<const T*>(a.kv) + h * DH + j * 8;
         pos_stride = (size_t)2 * d;
-        arow = a.anc + ((size_t)ctl->cur * a.M + r) * a.T_max;
     } else {
-        const int b = blockIdx.x, q0 = blockIdx.z * NQ;
-        row0 = b * a.beam + q0; nq = min(NQ, a.beam - q0);
-        n = (a.mem_len != nullptr) ? a.mem_len[b] : a.S;
-        kbase = reinterpret_cast<const T*>(a.kv) + ((size_t)b * a.S * a.L + a.layer) * 2 * d + h * DH;
+        kbase = reinterpret_cast<const T*>(a.kv) + ((size_t)b * a.S * a.L + a.layer) * 2 * d + h * DH + j * 8;
         pos_stride = (size_t)a.L * 2 * d;
     }
-    const int npad = (n + 3) & ~3;
-    float* sc = sm;                                      // [NQ][npad]
-    float* pv = sm + NQ * npad;                          // [AT_WARPS][NQ][DH]
-    float* inv = pv + AT_WARPS * NQ * DH;                // [NQ]
-    unsigned char* s_anc = reinterpret_cast<unsigned char*>(inv + NQ);     // SELF: [n] physical beam slot per position
-
-    if (SELF) {
-        // append this row's K,V (rounded to the cache type) at position pc, then treat it like any cached position
-        const int r = row0, pc = n - 1;
-        T* knew = reinterpret_cast<T*>(a.kv) + (((size_t)r * a.T_max + pc) * 2) * d + h * DH;
-        const float* qrow = a.q + (size_t)r * a.ldq + h * DH;
-        if (tid < DH) knew[tid] = from_f32<T>(qrow[d + tid]);
-        else knew[d + tid - DH] = from_f32<T>(qrow[2 * d + tid - DH]);
-        for (int p = tid; p < pc; p += AT_THREADS) s_anc[p] = arow[p];
-        if (tid == 0) s_anc[pc] = (unsigned char)(r % a.beam);
-        __syncthreads();
-    }
-    const int base = SELF ? (row0 / a.beam) * a.beam : 0;
-    auto kaddr = [&](int p) -> const T* {
-        if (SELF) return kbase + ((size_t)(base + s_anc[p]) * a.T_max + p) * pos_stride + j * 8;
-        return kbase + (size_t)p * pos_stride + j * 8;
+    const int slot_base = b * a.beam;
+    // K row (this lane's 8 dims) of position p as seen by slot qi; V row = K row + d
+    auto kaddr = [&](int qi, int p) -> const T* {
+        if (SELF) return kbase + ((size_t)(slot_base + s_anc[qi * n + p]) * a.T_max + p) * pos_stride;
+        return kbase + (size_t)p * pos_stride;
     };
-
-    // queries: this lane's 8 dims, pre-scaled by 1/sqrt(64) (exact: power of two)
     float qr[NQ][8];
 #pragma unroll
-    for (int qi = 0; qi < NQ; ++qi) {
-        const int r = row0 + min(qi, nq - 1);
-        const float4* q4 = reinterpret_cast<const float4*>(a.q + (size_t)r * a.ldq + h * DH + j * 8);
-        float4 x = q4[0], y = q4[1];
-        qr[qi][0] = x.x * 0.125f; qr[qi][1] = x.y * 0.125f; qr[qi][2] = x.z * 0.125f; qr[qi][3] = x.w * 0.125f;
-        qr[qi][4] = y.x * 0.125f; qr[qi][5] = y.y * 0.125f; qr[qi][6] = y.z * 0.125f; qr[qi][7] = y.w * 0.125f;
-    }
+    for (int qi = 0; qi < NQ; ++qi)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) qr[qi][e] = qs[qi * DH + j * 8 + e];
 
-    // ---- phase A: scores ----
-    for (int p0 = w * 16; p0 < n; p0 += AT_WARPS * 16) {
+    // ---- phase A: scores; shared positions [0,c): one K row serves all slots ----
+    for (int p0 = w * 16; p0 < c; p0 += AT_WARPS * 16) {
         Raw8<T> raw[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int p = p0 + u * 4 + g;
-            if (p < n) raw[u].load(kaddr(p));
+            if (p < c) raw[u].load(kaddr(0, p));
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int p = p0 + u * 4 + g;
             float kf[8];
-            if (p < n) raw[u].unpack(kf);
+            if (p < c) raw[u].unpack(kf);
             else {
 #pragma unroll
                 for (int e = 0; e < 8; ++e) kf[e] = 0.f;
@@ -150,16 +211,47 @@ __global__ void __launch_bounds__(AT_THREADS) attn_kernel(AttnArgs a) {
                 acc += __shfl_xor_sync(0xffffffffu, acc, 1);
                 acc += __shfl_xor_sync(0xffffffffu, acc, 2);
                 acc += __shfl_xor_sync(0xffffffffu, acc, 4);
-                if (j == 0 && p < n) {
+                if (j == 0 && p < c) {
                     // additive mask (1 - m) * -10000 : reference src/bert_seq2seq.py:36-37
-                    if (!SELF && a.mask != nullptr && a.mask[(size_t)blockIdx.x * a.S + p] == 0) acc += -10000.0f;
+                    if (!SELF && a.mask != nullptr && a.mask[(size_t)b * a.S + p] == 0) acc += -10000.0f;
                     sc[qi * npad + p] = acc;
                 }
             }
         }
     }
+    // divergent tail [c,n) (self-attention only): lane group g serves slot g, its positions dealt to the warps
+    float qd[8];
+    if (SELF && NQ > 1) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) qd[e] = qs[min(g, NQ - 1) * DH + j * 8 + e];
+        for (int p0 = c + w * 4; p0 < n; p0 += AT_WARPS * 4) {
+            Raw8<T> raw[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int p = p0 + u;
+                if (p < n && g < NQ) raw[u].load(kaddr(g, p));
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int p = p0 + u;
+                float kf[8];
+                if (p < n && g < NQ) raw[u].unpack(kf);
+                else {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) kf[e] = 0.f;
+                }
+                float acc = 0.f;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc = fmaf(kf[e], qd[e], acc);
+                acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+                acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+                acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+                if (j == 0 && p < n && g < NQ) sc[g * npad + p] = acc;
+            }
+        }
+    }
     __syncthreads();
-    // ---- phase B: softmax statistics, one warp per query ----
+    // ---- phase B: softmax statistics, one warp per slot ----
     for (int qi = w; qi < NQ; qi += AT_WARPS) {
         float* s = sc + qi * npad;
         float mx = -INFINITY;
@@ -181,17 +273,17 @@ __global__ void __launch_bounds__(AT_THREADS) attn_kernel(AttnArgs a) {
     for (int qi = 0; qi < NQ; ++qi)
 #pragma unroll
         for (int e = 0; e < 8; ++e) acc[qi][e] = 0.f;
-    for (int p0 = w * 16; p0 < n; p0 += AT_WARPS * 16) {
+    for (int p0 = w * 16; p0 < c; p0 += AT_WARPS * 16) {
         Raw8<T> raw[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int p = p0 + u * 4 + g;
-            if (p < n) raw[u].load(kaddr(p) + d);
+            if (p < c) raw[u].load(kaddr(0, p) + d);
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int p = p0 + u * 4 + g;
-            if (p < n) {
+            if (p < c) {
                 float vf[8];
                 raw[u].unpack(vf);
 #pragma unroll
@@ -212,6 +304,35 @@ __global__ void __launch_bounds__(AT_THREADS) attn_kernel(AttnArgs a) {
             v += __shfl_xor_sync(0xffffffffu, v, 16);
             if (g == 0) pv[(w * NQ + qi) * DH + j * 8 + k] = v;
         }
+    if (SELF && NQ > 1) {
+        float ad[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) ad[k] = 0.f;
+        for (int p0 = c + w * 4; p0 < n; p0 += AT_WARPS * 4) {
+            Raw8<T> raw[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int p = p0 + u;
+                if (p < n && g < NQ) raw[u].load(kaddr(g, p) + d);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int p = p0 + u;
+                if (p < n && g < NQ) {
+                    float vf[8];
+                    raw[u].unpack(vf);
+                    const float e = sc[g * npad + p];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) ad[k] = fmaf(e, vf[k], ad[k]);
+                }
+            }
+        }
+        __syncwarp();
+        if (g < NQ) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) pv[(w * NQ + g) * DH + j * 8 + k] += ad[k];
+        }
+    }
     __syncthreads();
     for (int i = tid; i < nq * DH; i += AT_THREADS) {
         const int qi = i / DH, k = i % DH;
@@ -224,20 +345,32 @@ __global__ void __launch_bounds__(AT_THREADS) attn_kernel(AttnArgs a) {
 
 template <typename T>
 static int launch_self(const AttnArgs& a, int H, cudaStream_t s) {
-    const size_t smem = ((size_t)((a.T_max + 3) & ~3) + AT_WARPS * DH + 1) * sizeof(float) + a.T_max + 16;
-    cudaError_t e = itb_launch(attn_kernel<T, 1, true>, dim3(a.M, H), dim3(AT_THREADS), smem, s, a);
+    const int B = a.M / a.beam;
+    const int np = (a.T_max + 3) & ~3;
+    cudaError_t e;
+    if (a.beam == 1) {
+        const size_t smem = ((size_t)np + AT_WARPS * DH + DH + 1) * sizeof(float) + a.T_max + 16;
+        e = itb_launch(attn_kernel<T, 1, true>, dim3(B, H, 1), dim3(AT_THREADS), smem, s, a);
+    } else {
+        const size_t smem = ((size_t)NQ_MAX * np + AT_WARPS * NQ_MAX * DH + NQ_MAX * DH + NQ_MAX) * sizeof(float) + (size_t)NQ_MAX * a.T_max + 16;
+        e = itb_launch(attn_kernel<T, NQ_MAX, true>, dim3(B, H, (a.beam + NQ_MAX - 1) / NQ_MAX), dim3(AT_THREADS), smem, s, a);
+    }
     if (e != cudaSuccess) { itb_set_error("self_attention: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("self_attention");
 }
 
 template <typename T>
 static int launch_cross(const AttnArgs& a, int H, cudaStream_t s) {
-    const size_t smem = ((size_t)NQ_MAX * ((a.S + 3) & ~3) + AT_WARPS * NQ_MAX * DH + NQ_MAX) * sizeof(float) + 16;
     const int B = a.M / a.beam;
+    const int np = (a.S + 3) & ~3;
     cudaError_t e;
-    if (a.beam == 1) e = itb_launch(attn_kernel<T, 1, false>, dim3(B, H, 1), dim3(AT_THREADS), smem, s, a);
-    else if (a.beam == 2) e = itb_launch(attn_kernel<T, 2, false>, dim3(B, H, 1), dim3(AT_THREADS), smem, s, a);
-    else e = itb_launch(attn_kernel<T, NQ_MAX, false>, dim3(B, H, (a.beam + NQ_MAX - 1) / NQ_MAX), dim3(AT_THREADS), smem, s, a);
+    if (a.beam == 1) {
+        const size_t smem = ((size_t)np + AT_WARPS * DH + DH + 1) * sizeof(float) + 16;
+        e = itb_launch(attn_kernel<T, 1, false>, dim3(B, H, 1), dim3(AT_THREADS), smem, s, a);
+    } else {
+        const size_t smem = ((size_t)NQ_MAX * np + AT_WARPS * NQ_MAX * DH + NQ_MAX * DH + NQ_MAX) * sizeof(float) + 16;
+        e = itb_launch(attn_kernel<T, NQ_MAX, false>, dim3(B, H, (a.beam + NQ_MAX - 1) / NQ_MAX), dim3(AT_THREADS), smem, s, a);
+    }
     if (e != cudaSuccess) { itb_set_error("cross_attention: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("cross_attention");
 }
@@ -248,6 +381,7 @@ int itb_self_attention(int dtype, const itb_ctl* ctl, const int* sent_done, cons
                        const unsigned char* anc, void* ctx, int M, int beam, int d, int H, int T_max, void* stream) {
     ITB_REQUIRE(d == H * DH, "self_attention: head_dim must be 64 (d == 64*H)");
     ITB_REQUIRE(T_max <= 2048, "self_attention: T_max too large for the shared-memory score buffer");
+    ITB_REQUIRE(M % beam == 0, "self_attention: M must be a multiple of the beam width");
     AttnArgs a = {};
     a.ctl = reinterpret_cast<const ItbCtl*>(ctl);
     a.sent_done = sent_done;

@@ -10,7 +10,8 @@
 //   warp 0   TMA producer  : cp.async.bulk.tensor 2D (SWIZZLE_128B) W[128x64] + A[MTx64] per stage
 //   warp 1   MMA issuer    : one thread, 4 x tcgen05.mma (K=16) per stage, fp32 accumulators in TMEM
 //   warp 2   TMEM allocator
-//   warps 4-7 epilogue     : tcgen05.ld 32x32b -> +bias (-> GELU) -> coalesced global stores
+//   warps 4-11 epilogue    : tcgen05.ld 32x32b -> +bias (-> GELU) -> coalesced global stores; two warps per TMEM lane
+//                            quarter, each taking half of the tile's columns
 // Persistent CTAs (grid = #SMs) walk the tile list; TMEM accumulators are double-buffered so the
 // epilogue of tile i overlaps the MMAs/loads of tile i+1.
 #include <cuda.h>
@@ -19,7 +20,7 @@
 
 #define TC_BN 128          // weight rows per tile (UMMA M)
 #define TC_BK 64           // K per stage: 64 bf16 = one 128-byte swizzle row
-#define TC_THREADS 256
+#define TC_THREADS 384      // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-11 epilogue (two warps per TMEM lane quarter)
 #define TC_SPIN_LIMIT (1u << 28)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -129,7 +130,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < Cfg::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 128); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 256); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -209,6 +210,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         }
     } else if (warp >= 4) {
         const int q = warp & 3;                                 // TMEM lane quarter this warp may access
+        const int half = (warp - 4) >> 2;                       // which half of the tile's columns this warp drains
+        constexpr int CH = (MT / 2 < 32) ? 32 : MT / 2;         // MT = 32: the second warp of the quarter has no columns
         uint32_t as = 0, aphase = 0;
         for (int t = blockIdx.x; t < total; t += gridDim.x) {
             const int ks = t % nsplit, mt = (t / nsplit) % m_tiles, nt = (t / nsplit) / m_tiles;
@@ -218,10 +221,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
             const float bv = (n < N && bias != nullptr && ks == 0) ? bias[n] : 0.f;
             float* outp = reinterpret_cast<float*>(out) + (size_t)ks * part_stride;      // split-K partial (f32 epilogue only)
 #pragma unroll 1
-            for (int c0 = 0; c0 < MT; c0 += 32) {
+            for (int c0 = half * CH; c0 < (half + 1) * CH && c0 < MT; c0 += 32) {
+                const int mbase = mt * MT + c0;
+                if (mbase >= M) break;                              // rows past M (zero-filled by TMA): nothing to store
                 uint32_t v[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * MT + c0, v);
-                const int mbase = mt * MT + c0;
                 if (n < N) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {

@@ -3,84 +3,120 @@
 #include "common.cuh"
 #include "launch.h"
 
-// LayerNorm over `d` values held in shared memory `row`; writes f32 + act copies.
-template <typename TA>
-__device__ __forceinline__ void ln_write(const float* row, int d, const float* __restrict__ g,
-                                         const float* __restrict__ b, float eps, float* __restrict__ of,
-                                         TA* __restrict__ oa, float* red) {
-    float s = 0.f;
-    for (int i = threadIdx.x; i < d; i += blockDim.x) s += row[i];
-    float mean = block_sum(s, red) / (float)d;
-    float v = 0.f;
-    for (int i = threadIdx.x; i < d; i += blockDim.x) { float t = row[i] - mean; v += t * t; }
-    float var = block_sum(v, red) / (float)d;
-    float rstd = rsqrtf(var + eps);
-    for (int i = threadIdx.x; i < d; i += blockDim.x) {
-        float o = (row[i] - mean) * rstd * g[i] + b[i];
-        of[i] = o;
-        oa[i] = from_f32<TA>(o);
-    }
+// One WARP per row (d = 768 -> 24 values per lane, kept in registers), LN_ROWS rows per CTA: no shared memory, no block
+// barrier; mean and variance by warp shuffles in fp32, two-pass (mean first, then centred squares) as torch.layer_norm.
+#define LN_ROWS 8
+#define LN_MAXV 8        // float4 per lane: d <= 32 * 4 * LN_MAXV = 1024
+
+__device__ __forceinline__ void store4(float* p, float4 o) { *reinterpret_cast<float4*>(p) = o; }
+__device__ __forceinline__ void store4(__nv_bfloat16* p, float4 o) {
+    uint2 u;
+    *reinterpret_cast<__nv_bfloat162*>(&u.x) = __floats2bfloat162_rn(o.x, o.y);
+    *reinterpret_cast<__nv_bfloat162*>(&u.y) = __floats2bfloat162_rn(o.z, o.w);
+    *reinterpret_cast<uint2*>(p) = u;
+}
+__device__ __forceinline__ void store4(__half* p, float4 o) {
+    uint2 u;
+    *reinterpret_cast<__half2*>(&u.x) = __floats2half2_rn(o.x, o.y);
+    *reinterpret_cast<__half2*>(&u.y) = __floats2half2_rn(o.z, o.w);
+    *reinterpret_cast<uint2*>(p) = u;
 }
 
 template <typename TA>
-__global__ void __launch_bounds__(256) embed_ln_kernel(const ItbCtl* __restrict__ ctl, const int* __restrict__ tokens,
+__device__ __forceinline__ void ln_row_write(float4* v, int nv, int d, const float* __restrict__ g, const float* __restrict__ b,
+                                             float eps, float* __restrict__ of, TA* __restrict__ oa, int lane) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i)
+        if (i < nv) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    const float mean = warp_sum(s) / (float)d;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i)
+        if (i < nv) {
+            float a0 = v[i].x - mean, a1 = v[i].y - mean, a2 = v[i].z - mean, a3 = v[i].w - mean;
+            q += (a0 * a0 + a1 * a1) + (a2 * a2 + a3 * a3);
+        }
+    const float rstd = rsqrtf(warp_sum(q) / (float)d + eps);
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i)
+        if (i < nv) {
+            const int c = (i * 32 + lane) * 4;
+            if (c < d) {
+                const float4 gg = *reinterpret_cast<const float4*>(g + c), bb = *reinterpret_cast<const float4*>(b + c);
+                float4 o;
+                o.x = (v[i].x - mean) * rstd * gg.x + bb.x;
+                o.y = (v[i].y - mean) * rstd * gg.y + bb.y;
+                o.z = (v[i].z - mean) * rstd * gg.z + bb.z;
+                o.w = (v[i].w - mean) * rstd * gg.w + bb.w;
+                *reinterpret_cast<float4*>(of + c) = o;
+                store4(oa + c, o);
+            }
+        }
+}
+
+template <typename TA>
+__global__ void __launch_bounds__(32 * LN_ROWS) embed_ln_kernel(const ItbCtl* __restrict__ ctl, const int* __restrict__ tokens,
                                                        const int* __restrict__ tgt_lang, const float* __restrict__ word,
                                                        const float* __restrict__ pos, const float* __restrict__ type,
                                                        const float* __restrict__ g, const float* __restrict__ b, float eps,
                                                        float* __restrict__ x_f32, TA* __restrict__ x_act, int M, int beam,
                                                        int d, int T_max) {
-    extern __shared__ float sm[];
-    float* row = sm;
-    float* red = sm + d;
     pdl_trigger();
     pdl_wait();
-    if (ctl->done) return;
-    const int r = blockIdx.x;
-    const int p = ctl->step - 1;                     // 0-based position of the token consumed this step
-    const int tok = tokens[((size_t)ctl->cur * M + r) * T_max + p];
+    const int4 c4 = *reinterpret_cast<const int4*>(ctl);          // {step, done, steps_run, cur}
+    if (c4.y != 0) return;
+    const int lane = threadIdx.x & 31, r = blockIdx.x * LN_ROWS + (threadIdx.x >> 5);
+    if (r >= M) return;
+    const int p = c4.x - 1;                          // 0-based position of the token consumed this step
+    const int tok = tokens[((size_t)c4.w * M + r) * T_max + p];
     const int lang = tgt_lang[r / beam];
-    const float4* w4 = reinterpret_cast<const float4*>(word + (size_t)tok * d);
-    const float4* p4 = reinterpret_cast<const float4*>(pos + (size_t)p * d);
-    const float4* t4 = reinterpret_cast<const float4*>(type + (size_t)lang * d);
-    for (int i = threadIdx.x; i < d / 4; i += blockDim.x) {
-        float4 a = w4[i], c = p4[i], e = t4[i];
-        row[4 * i + 0] = a.x + c.x + e.x;
-        row[4 * i + 1] = a.y + c.y + e.y;
-        row[4 * i + 2] = a.z + c.z + e.z;
-        row[4 * i + 3] = a.w + c.w + e.w;
+    const int nv = (d + 127) / 128;
+    float4 v[LN_MAXV];
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i) {
+        const int c = (i * 32 + lane) * 4;
+        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < nv && c < d) {
+            const float4 a = *reinterpret_cast<const float4*>(word + (size_t)tok * d + c);
+            const float4 e = *reinterpret_cast<const float4*>(pos + (size_t)p * d + c);
+            const float4 t = *reinterpret_cast<const float4*>(type + (size_t)lang * d + c);
+            v[i] = make_float4(a.x + e.x + t.x, a.y + e.y + t.y, a.z + e.z + t.z, a.w + e.w + t.w);
+        }
     }
-    __syncthreads();
-    ln_write<TA>(row, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, red);
+    // lanes past d hold zeros, which the centred second pass must not count: handled by c < d on load and the exact
+    // mean (sum / d); the variance pass subtracts the mean from padded zeros, so d must be a multiple of 128
+    ln_row_write<TA>(v, nv, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, lane);
 }
 
 template <typename TA>
-__global__ void __launch_bounds__(256) add_ln_kernel(const ItbCtl* __restrict__ ctl, const float* __restrict__ y,
+__global__ void __launch_bounds__(32 * LN_ROWS) add_ln_kernel(const ItbCtl* __restrict__ ctl, const float* __restrict__ y,
                                                      int n_partial, const float* __restrict__ g,
                                                      const float* __restrict__ b, float eps, float* __restrict__ x_f32,
                                                      TA* __restrict__ x_act, int M, int d) {
-    extern __shared__ float sm[];
-    float* row = sm;
-    float* red = sm + d;
     pdl_trigger();
     pdl_wait();
     if (ctl != nullptr && ctl->done) return;
-    const int r = blockIdx.x;
-    const float4* x4 = reinterpret_cast<const float4*>(x_f32 + (size_t)r * d);
-    for (int i = threadIdx.x; i < d / 4; i += blockDim.x) {
-        // y = sum of the split-K partial outputs of the producing GEMM, in a fixed order (deterministic)
-        float4 a = reinterpret_cast<const float4*>(y + (size_t)r * d)[i];
-        for (int sp = 1; sp < n_partial; ++sp) {
-            float4 t = reinterpret_cast<const float4*>(y + ((size_t)sp * M + r) * d)[i];
-            a.x += t.x; a.y += t.y; a.z += t.z; a.w += t.w;
+    const int lane = threadIdx.x & 31, r = blockIdx.x * LN_ROWS + (threadIdx.x >> 5);
+    if (r >= M) return;
+    const int nv = (d + 127) / 128;
+    float4 v[LN_MAXV];
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i) {
+        const int c = (i * 32 + lane) * 4;
+        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < nv && c < d) {
+            // y = sum of the split-K partial outputs of the producing GEMM, in a fixed order (deterministic)
+            float4 a = *reinterpret_cast<const float4*>(y + (size_t)r * d + c);
+            for (int sp = 1; sp < n_partial; ++sp) {
+                const float4 t = *reinterpret_cast<const float4*>(y + ((size_t)sp * M + r) * d + c);
+                a.x += t.x; a.y += t.y; a.z += t.z; a.w += t.w;
+            }
+            const float4 x = *reinterpret_cast<const float4*>(x_f32 + (size_t)r * d + c);
+            v[i] = make_float4(a.x + x.x, a.y + x.y, a.z + x.z, a.w + x.w);
         }
-        float4 c = x4[i];
-        row[4 * i + 0] = a.x + c.x;
-        row[4 * i + 1] = a.y + c.y;
-        row[4 * i + 2] = a.z + c.z;
-        row[4 * i + 3] = a.w + c.w;
     }
-    __syncthreads();
-    ln_write<TA>(row, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, red);
+    ln_row_write<TA>(v, nv, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, lane);
 }
 
 // seq_gen.py:109-123: prefix = first token in every slot, scores 0, sizes 0; ancestors = own slot.
@@ -167,19 +203,20 @@ extern "C" {
 int itb_embed_ln(int dtype, const itb_ctl* ctl, const int* tokens, const int* tgt_lang, const float* word,
                  const float* pos, const float* type, const float* g, const float* b, float eps, float* x_f32,
                  void* x_act, int M, int beam, int d, int T_max, void* stream) {
-    ITB_REQUIRE(d % 4 == 0 && M > 0, "embed_ln: d must be a multiple of 4");
-    size_t smem = (d + 32) * sizeof(float);
+    ITB_REQUIRE(d % 128 == 0 && d <= 1024 && M > 0, "embed_ln: d must be a multiple of 128, at most 1024");
+    const size_t smem = 0;
+    const dim3 lgrid((M + LN_ROWS - 1) / LN_ROWS), lblock(32 * LN_ROWS);
     cudaStream_t s = (cudaStream_t)stream;
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
     cudaError_t e;
     if (dtype == ITB_BF16)
-        e = itb_launch(embed_ln_kernel<__nv_bfloat16>, dim3(M), dim3(256), smem, s, c, tokens, tgt_lang, word, pos, type, g, b,
+        e = itb_launch(embed_ln_kernel<__nv_bfloat16>, lgrid, lblock, smem, s, c, tokens, tgt_lang, word, pos, type, g, b,
                        eps, x_f32, (__nv_bfloat16*)x_act, M, beam, d, T_max);
     else if (dtype == ITB_F16)
-        e = itb_launch(embed_ln_kernel<__half>, dim3(M), dim3(256), smem, s, c, tokens, tgt_lang, word, pos, type, g, b, eps,
+        e = itb_launch(embed_ln_kernel<__half>, lgrid, lblock, smem, s, c, tokens, tgt_lang, word, pos, type, g, b, eps,
                        x_f32, (__half*)x_act, M, beam, d, T_max);
     else
-        e = itb_launch(embed_ln_kernel<float>, dim3(M), dim3(256), smem, s, c, tokens, tgt_lang, word, pos, type, g, b, eps,
+        e = itb_launch(embed_ln_kernel<float>, lgrid, lblock, smem, s, c, tokens, tgt_lang, word, pos, type, g, b, eps,
                        x_f32, (float*)x_act, M, beam, d, T_max);
     if (e != cudaSuccess) { itb_set_error("embed_ln: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("embed_ln");
@@ -187,19 +224,20 @@ int itb_embed_ln(int dtype, const itb_ctl* ctl, const int* tokens, const int* tg
 
 int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, int n_partial, const float* g, const float* b, float eps,
                float* x_f32, void* x_act, int M, int d, void* stream) {
-    ITB_REQUIRE(d % 4 == 0 && M > 0, "add_ln: d must be a multiple of 4");
+    ITB_REQUIRE(d % 128 == 0 && d <= 1024 && M > 0, "add_ln: d must be a multiple of 128, at most 1024");
     ITB_REQUIRE(n_partial >= 1, "add_ln: n_partial must be >= 1");
-    size_t smem = (d + 32) * sizeof(float);
+    const size_t smem = 0;
+    const dim3 lgrid((M + LN_ROWS - 1) / LN_ROWS), lblock(32 * LN_ROWS);
     cudaStream_t s = (cudaStream_t)stream;
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
     cudaError_t e;
     if (dtype == ITB_BF16)
-        e = itb_launch(add_ln_kernel<__nv_bfloat16>, dim3(M), dim3(256), smem, s, c, y, n_partial, g, b, eps, x_f32,
+        e = itb_launch(add_ln_kernel<__nv_bfloat16>, lgrid, lblock, smem, s, c, y, n_partial, g, b, eps, x_f32,
                        (__nv_bfloat16*)x_act, M, d);
     else if (dtype == ITB_F16)
-        e = itb_launch(add_ln_kernel<__half>, dim3(M), dim3(256), smem, s, c, y, n_partial, g, b, eps, x_f32, (__half*)x_act, M, d);
+        e = itb_launch(add_ln_kernel<__half>, lgrid, lblock, smem, s, c, y, n_partial, g, b, eps, x_f32, (__half*)x_act, M, d);
     else
-        e = itb_launch(add_ln_kernel<float>, dim3(M), dim3(256), smem, s, c, y, n_partial, g, b, eps, x_f32, (float*)x_act, M, d);
+        e = itb_launch(add_ln_kernel<float>, lgrid, lblock, smem, s, c, y, n_partial, g, b, eps, x_f32, (float*)x_act, M, d);
     if (e != cudaSuccess) { itb_set_error("add_ln: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("add_ln");
 }

@@ -104,7 +104,12 @@ def test_self_attention_through_ancestor_table(dtype, step):
     qkv = _rand((M, 3 * d), 11)
     kv = _rand((M, T, 2, d), 12).to(act)
     g = torch.Generator().manual_seed(13)
-    anc = torch.randint(0, beam, (2, M, T), generator=g).to(torch.uint8).to(DEV)
+    anc = torch.randint(0, beam, (2, M, T), generator=g)
+    # lineages of a sentence's slots share their physical rows before they split (sentence 0: at 25, sentence 1: never
+    # shared, sentence 2: shared up to the current position)
+    anc[:, 0:beam, :25] = anc[:, 0:1, :25]
+    anc[:, 2 * beam:3 * beam, :] = anc[:, 2 * beam:2 * beam + 1, :]
+    anc = anc.to(torch.uint8).to(DEV)
     ctl = make_ctl(step=step, cur=1)
     ctx = torch.zeros(M, d, device=DEV, dtype=act)
     kv_before = kv.clone()

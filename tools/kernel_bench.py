@@ -88,7 +88,10 @@ total += 3 * L * bench("add_ln", lambda i: _lib.check(lib.itb_add_ln(DT, _lib.pt
 # self attention at position t-1
 qkv = rnd(M, 3 * d)
 kv = [rnd(M, T, 2, d, dt=ACT) for _ in range(NB)]
-anc = torch.randint(0, beam, (2, M, T), device=DEV).to(torch.uint8)
+anc = torch.randint(0, beam, (2, M, T), device=DEV)
+SHARE = int(os.environ.get("KB_SHARE", max(t - 6, 0)))      # positions before which the slots of a sentence share rows
+anc[:, :, :SHARE] = anc.view(2, B, beam, T)[:, :, :1, :SHARE].expand(2, B, beam, SHARE).reshape(2, M, SHARE)
+anc = anc.to(torch.uint8)
 ctx = torch.empty(M, d, dtype=ACT, device=DEV)
 esz = kv[0].element_size()
 total += L * bench("self_attn t=%d" % t, lambda i: _lib.check(lib.itb_self_attention(DT, _lib.ptr(ctl), None, _lib.ptr(qkv), _lib.ptr(kv[i]),
