@@ -79,3 +79,20 @@ template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(flo
 
 // exact (erf) GELU, as HF "gelu" (transformers 2.9.0 BertIntermediate)
 __device__ __forceinline__ float gelu_erf(float x) { return x * 0.5f * (1.0f + erff(x * 0.70710678118654752440f)); }
+
+// erf GELU for the 16-bit tensor-core epilogues, one MUFU and no branch: erf(z) = 1 - (1 + a1 z + ... + a6 z^6)^-16
+// (Abramowitz-Stegun 7.1.28, |error| <= 3e-7; GELU abs error < 1e-6, far below the bf16/fp16 rounding of the result).
+// The fp32 parity path keeps erff (gelu_erf).
+__device__ __forceinline__ float gelu_erf_fast(float x) {
+    const float z = fabsf(x) * 0.70710678118654752440f;
+    float p = fmaf(z, 0.0000430638f, 0.0002765672f);
+    p = fmaf(z, p, 0.0001520143f);
+    p = fmaf(z, p, 0.0092705272f);
+    p = fmaf(z, p, 0.0422820123f);
+    p = fmaf(z, p, 0.0705230784f);
+    p = fmaf(z, p, 1.0f);
+    p *= p; p *= p; p *= p; p *= p;                       // ^16 (overflows to +inf for z > ~17: erf = 1, as it should)
+    const float e = 1.0f - __fdividef(1.0f, p);
+    const float hx = 0.5f * x;
+    return fmaf(hx, copysignf(e, x), hx);
+}

@@ -100,6 +100,58 @@ template <int MT> struct TcCfg {
     static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 };
 
+// Epilogue of warps 4-11: TMEM lane = weight row n (this lane), TMEM column = activation row m.  Per 32-column chunk one
+// tcgen05.ld, then 32 stores out[m][n] that are coalesced across the warp (consecutive n); the row pointer advances by
+// ldo per column, full chunks take a path without per-element bounds checks.
+template <int MT, int EPI, typename OT>
+__device__ __forceinline__ void tc_epilogue(uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty, const float* __restrict__ bias,
+                                            OT* __restrict__ out, int M, int N, int ldo, int nsplit, size_t part_stride,
+                                            int total, int m_tiles, int warp, int lane) {
+    const int q = warp & 3;                                 // TMEM lane quarter this warp may access
+    const int half = (warp - 4) >> 2;                       // which half of the tile's columns this warp drains
+    constexpr int CH = (MT / 2 < 32) ? 32 : MT / 2;         // MT = 32: the second warp of the quarter has no columns
+    uint32_t as = 0, aphase = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const int ks = t % nsplit, mt = (t / nsplit) % m_tiles, nt = (t / nsplit) / m_tiles;
+        mbar_wait(&tfull[as], aphase);
+        tc_fence_after();
+        const int n = nt * TC_BN + q * 32 + lane;
+        const float bv = (n < N && bias != nullptr && ks == 0) ? bias[n] : 0.f;
+        OT* outp = out + (size_t)ks * part_stride;          // split-K partial (f32 epilogue only)
+#pragma unroll 1
+        for (int c0 = half * CH; c0 < (half + 1) * CH && c0 < MT; c0 += 32) {
+            const int mbase = mt * MT + c0;
+            if (mbase >= M) break;                              // rows past M (zero-filled by TMA): nothing to store
+            uint32_t v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * MT + c0, v);
+            if (n < N) {
+                OT* p = outp + (size_t)mbase * ldo + n;
+                if (mbase + 32 <= M) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        float x = __uint_as_float(v[j]) + bv;
+                        if (EPI == ITB_EPI_BIAS_GELU_ACT) x = gelu_erf_fast(x);
+                        p[(size_t)j * ldo] = from_f32<OT>(x);
+                    }
+                } else {
+                    const int rows = M - mbase;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {          // fully unrolled: v[] must stay in registers
+                        if (j < rows) {
+                            float x = __uint_as_float(v[j]) + bv;
+                            if (EPI == ITB_EPI_BIAS_GELU_ACT) x = gelu_erf_fast(x);
+                            p[(size_t)j * ldo] = from_f32<OT>(x);
+                        }
+                    }
+                }
+            }
+        }
+        tc_fence_before();
+        mbar_arrive(&tempty[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+}
+
 template <int MT, int EPI>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
@@ -209,43 +261,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
             }
         }
     } else if (warp >= 4) {
-        const int q = warp & 3;                                 // TMEM lane quarter this warp may access
-        const int half = (warp - 4) >> 2;                       // which half of the tile's columns this warp drains
-        constexpr int CH = (MT / 2 < 32) ? 32 : MT / 2;         // MT = 32: the second warp of the quarter has no columns
-        uint32_t as = 0, aphase = 0;
-        for (int t = blockIdx.x; t < total; t += gridDim.x) {
-            const int ks = t % nsplit, mt = (t / nsplit) % m_tiles, nt = (t / nsplit) / m_tiles;
-            mbar_wait(&tfull[as], aphase);
-            tc_fence_after();
-            const int n = nt * TC_BN + q * 32 + lane;
-            const float bv = (n < N && bias != nullptr && ks == 0) ? bias[n] : 0.f;
-            float* outp = reinterpret_cast<float*>(out) + (size_t)ks * part_stride;      // split-K partial (f32 epilogue only)
-#pragma unroll 1
-            for (int c0 = half * CH; c0 < (half + 1) * CH && c0 < MT; c0 += 32) {
-                const int mbase = mt * MT + c0;
-                if (mbase >= M) break;                              // rows past M (zero-filled by TMA): nothing to store
-                uint32_t v[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * MT + c0, v);
-                if (n < N) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const int m = mbase + j;
-                        if (m < M) {
-                            float x = __uint_as_float(v[j]) + bv;
-                            if (EPI == ITB_EPI_BIAS_F32) outp[(size_t)m * ldo + n] = x;
-                            else {
-                                if (EPI == ITB_EPI_BIAS_GELU_ACT) x = gelu_erf(x);
-                                if (act_f16) reinterpret_cast<__half*>(out)[(size_t)m * ldo + n] = __float2half_rn(x);
-                                else reinterpret_cast<__nv_bfloat16*>(out)[(size_t)m * ldo + n] = __float2bfloat16_rn(x);
-                            }
-                        }
-                    }
-                }
-            }
-            tc_fence_before();
-            mbar_arrive(&tempty[as]);
-            if (++as == 2) { as = 0; aphase ^= 1; }
-        }
+        if (EPI == ITB_EPI_BIAS_F32) tc_epilogue<MT, EPI, float>(tmem_base, tfull, tempty, bias, reinterpret_cast<float*>(out), M, N, ldo, nsplit, part_stride, total, m_tiles, warp, lane);
+        else if (act_f16) tc_epilogue<MT, EPI, __half>(tmem_base, tfull, tempty, bias, reinterpret_cast<__half*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane);
+        else tc_epilogue<MT, EPI, __nv_bfloat16>(tmem_base, tfull, tempty, bias, reinterpret_cast<__nv_bfloat16*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane);
     }
 
     tc_fence_before();
