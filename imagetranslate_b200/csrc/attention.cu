@@ -15,6 +15,7 @@
 //   phase C  sum_p e_p * V[p], reduced over lanes and warps, normalised, stored in the activation type.
 // Self-attention appends the rows' new K,V to the cache first.  HBM-bound: 2*d*sizeof(T) bytes per (hypothesis
 // lineage, position, layer) for self-attention, per (sentence, position, layer) for cross-attention.
+#include <stdlib.h>
 #include "common.cuh"
 #include "launch.h"
 
@@ -375,6 +376,20 @@ static int launch_cross(const AttnArgs& a, int H, cudaStream_t s) {
     return itb_check_launch("cross_attention");
 }
 
+int itb_attn_mma(int dtype, bool self, const void* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
+                 void* kv, const unsigned char* anc, const unsigned char* mask, void* ctx, int M, int beam, int d, int T_max,
+                 int S, int L, int layer, cudaStream_t s);
+
+// 16-bit modes run the tensor-core kernel (attention_mma.cu); fp32 (parity mode) and ITB_ATTN=simt run the CUDA-core one.
+static bool use_mma(int dtype) {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("ITB_ATTN");
+        v = (e != nullptr && e[0] == 's') ? 0 : 1;
+    }
+    return v != 0 && dtype != ITB_F32;
+}
+
 extern "C" {
 
 int itb_self_attention(int dtype, const itb_ctl* ctl, const int* sent_done, const float* qkv, void* kv_layer,
@@ -382,6 +397,9 @@ int itb_self_attention(int dtype, const itb_ctl* ctl, const int* sent_done, cons
     ITB_REQUIRE(d == H * DH, "self_attention: head_dim must be 64 (d == 64*H)");
     ITB_REQUIRE(T_max <= 2048, "self_attention: T_max too large for the shared-memory score buffer");
     ITB_REQUIRE(M % beam == 0, "self_attention: M must be a multiple of the beam width");
+    if (use_mma(dtype))
+        return itb_attn_mma(dtype, true, ctl, sent_done, nullptr, qkv, 3 * d, kv_layer, anc, nullptr, ctx, M, beam, d, T_max, 0, 0, 0,
+                            (cudaStream_t)stream);
     AttnArgs a = {};
     a.ctl = reinterpret_cast<const ItbCtl*>(ctl);
     a.sent_done = sent_done;
@@ -398,6 +416,9 @@ int itb_cross_attention(int dtype, const itb_ctl* ctl, const int* sent_done, con
     ITB_REQUIRE(d == H * DH, "cross_attention: head_dim must be 64 (d == 64*H)");
     ITB_REQUIRE(S <= 2048, "cross_attention: S too large for the shared-memory score buffer");
     ITB_REQUIRE(M % beam == 0, "cross_attention: M must be a multiple of the beam width");
+    if (use_mma(dtype))
+        return itb_attn_mma(dtype, false, ctl, sent_done, mem_len, q, ldq, const_cast<void*>(cross_kv), nullptr, src_mask, ctx, M, beam, d,
+                            0, S, L, layer, (cudaStream_t)stream);
     AttnArgs a = {};
     a.ctl = reinterpret_cast<const ItbCtl*>(ctl);
     a.sent_done = sent_done; a.mem_len = mem_len;
