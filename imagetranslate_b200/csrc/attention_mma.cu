@@ -25,6 +25,9 @@
 #define DH 64
 #define AM_WARPS 4
 #define AM_THREADS (AM_WARPS * 32)
+#define AM_STAGE 64            // virtual positions staged in shared memory per round trip
+#define AM_ROWB 272            // bytes per staged row: K 128 + V 128 + 16 pad
+#define AM_SMEM (AM_WARPS * AM_STAGE * AM_ROWB)
 
 struct AttnMmaArgs {
     const ItbCtl* ctl;
@@ -73,34 +76,46 @@ __device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t&
 }
 
 template <typename T, bool SELF>
-__global__ void __launch_bounds__(AM_THREADS, 4) attn_mma_kernel(AttnMmaArgs a) {
+__global__ void __launch_bounds__(AM_THREADS, 3) attn_mma_kernel(AttnMmaArgs a) {
     pdl_trigger();
     pdl_wait();
     const int lane = threadIdx.x & 31, nl = lane >> 2, c = lane & 3;       // nl: B-fragment column / C row; c: quad lane
     const int wg = blockIdx.x * AM_WARPS + (threadIdx.x >> 5);
     if (wg >= a.n_warps) return;
-    int4 c4 = make_int4(1, 0, 0, 0);                     // {step, done, steps_run, cur}
-    if (a.ctl != nullptr) c4 = *reinterpret_cast<const int4*>(a.ctl);
-    if (c4.y != 0) return;
     const int d = a.d, H = d / DH, nz = (a.beam + 3) >> 2;
     const int h = wg % H, z = (wg / H) % nz, b = wg / (H * nz);
-    if (a.sent_done != nullptr && a.sent_done[b] != 0) return;
     const int q0 = z * 4, row0 = b * a.beam + q0, nq = min(4, a.beam - q0);
-    const int n = SELF ? c4.x : ((a.mem_len != nullptr) ? a.mem_len[b] : a.S);   // self: positions 0..step-1
     const int hoff = h * DH;
+    // ---- first round trip: everything whose address depends on the warp index only (control words, the query row,
+    //      the row's new K,V) is requested before anything is consumed ----
+    int4 c4 = make_int4(1, 0, 0, 0);                     // {step, done, steps_run, cur}
+    if (a.ctl != nullptr) c4 = *reinterpret_cast<const int4*>(a.ctl);
+    const int sdone = (a.sent_done != nullptr) ? a.sent_done[b] : 0;
+    int n = a.S;
+    if (!SELF && a.mem_len != nullptr) n = a.mem_len[b];
+    float4 qx[4], kx[4], vx[4];
+    {
+        const float4* qp = reinterpret_cast<const float4*>(a.q + (size_t)(row0 + min(nl, nq - 1)) * a.ldq + hoff + 16 * c);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) qx[i] = qp[i];
+        if (SELF) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { kx[i] = qp[d / 4 + i]; vx[i] = qp[d / 2 + i]; }
+        }
+    }
+    if (c4.y != 0 || sdone != 0) return;
+    if (SELF) n = c4.x;                                  // self: positions 0..step-1
 
     // ---- Q fragments: row nl (< nq) of the A operand, dims [16c,16c+16) in k-slice order, scaled by 1/8, hi + lo ----
     uint32_t qhi[8], qlo[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { qhi[i] = 0u; qlo[i] = 0u; }
-    if (nl < nq) {
-        const float4* qp = reinterpret_cast<const float4*>(a.q + (size_t)(row0 + nl) * a.ldq + hoff + 16 * c);
+    for (int i = 0; i < 4; ++i) {
+        split2<T>(qx[i].x * 0.125f, qx[i].y * 0.125f, qhi[2 * i], qlo[2 * i]);
+        split2<T>(qx[i].z * 0.125f, qx[i].w * 0.125f, qhi[2 * i + 1], qlo[2 * i + 1]);
+    }
+    if (nl >= nq) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const float4 x = qp[i];
-            split2<T>(x.x * 0.125f, x.y * 0.125f, qhi[2 * i], qlo[2 * i]);
-            split2<T>(x.z * 0.125f, x.w * 0.125f, qhi[2 * i + 1], qlo[2 * i + 1]);
-        }
+        for (int i = 0; i < 8; ++i) { qhi[i] = 0u; qlo[i] = 0u; }
     }
 
     // ---- geometry of the virtual position list ----
@@ -115,22 +130,16 @@ __global__ void __launch_bounds__(AM_THREADS, 4) attn_mma_kernel(AttnMmaArgs a) 
         anc0 = a.anc + ((size_t)c4.w * a.M + row0) * a.T_max;
         // append the new K,V of the group's rows at position pc: lane (nl < nq, c) owns dims [16c,16c+16) of row nl
         if (nl < nq) {
-            const float* kp = a.q + (size_t)(row0 + nl) * a.ldq + d + hoff + 16 * c;
             T* dst = reinterpret_cast<T*>(a.kv) + ((size_t)(row0 + nl) * a.T_max + pc) * pos_stride + hoff + 16 * c;
+            uint32_t w[8];
 #pragma unroll
-            for (int kvsel = 0; kvsel < 2; ++kvsel) {
-                const float4* sp = reinterpret_cast<const float4*>(kp + kvsel * d);
-                uint32_t w[8];
+            for (int i = 0; i < 4; ++i) { w[2 * i] = Mma16<T>::pack(kx[i].x, kx[i].y); w[2 * i + 1] = Mma16<T>::pack(kx[i].z, kx[i].w); }
+            reinterpret_cast<uint4*>(dst)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+            reinterpret_cast<uint4*>(dst)[1] = make_uint4(w[4], w[5], w[6], w[7]);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float4 x = sp[i];
-                    w[2 * i] = Mma16<T>::pack(x.x, x.y);
-                    w[2 * i + 1] = Mma16<T>::pack(x.z, x.w);
-                }
-                uint4* dp = reinterpret_cast<uint4*>(dst + kvsel * d);
-                dp[0] = make_uint4(w[0], w[1], w[2], w[3]);
-                dp[1] = make_uint4(w[4], w[5], w[6], w[7]);
-            }
+            for (int i = 0; i < 4; ++i) { w[2 * i] = Mma16<T>::pack(vx[i].x, vx[i].y); w[2 * i + 1] = Mma16<T>::pack(vx[i].z, vx[i].w); }
+            reinterpret_cast<uint4*>(dst + d)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+            reinterpret_cast<uint4*>(dst + d)[1] = make_uint4(w[4], w[5], w[6], w[7]);
         }
         // first position whose physical row differs between the group's slots
         cshared = pc;
@@ -161,111 +170,128 @@ __global__ void __launch_bounds__(AM_THREADS, 4) attn_mma_kernel(AttnMmaArgs a) 
     float m_run = -INFINITY, l_run = 0.f;
     const int qrow = nl & 3;             // rows 4..7 mirror rows 0..3 (their results are discarded)
 
-    for (int vb = 0; vb < nv; vb += 32) {
-        // ---- virtual position vb + lane: row index and meta = owner mask (bits 0-3) | masked-source flag (bit 4) ----
-        int rowidx = -1, meta = 0;
-        {
-            const int v = vb + lane;
+    // Per-warp staging buffer: AM_STAGE virtual rows of [K 128 B | V 128 B], padded to 272 B so that the fragment reads
+    // below are bank-conflict free.  All rows of a stage are requested with cp.async (16 B each, zero-filled when the
+    // virtual position does not exist) BEFORE anything is consumed: one memory round trip per 64 positions, no
+    // registers tied up by loads in flight.
+    extern __shared__ __align__(16) unsigned char am_smem[];
+    unsigned char* ws = am_smem + (size_t)(threadIdx.x >> 5) * (AM_STAGE * AM_ROWB);
+    const uint32_t ws_u32 = (uint32_t)__cvta_generic_to_shared(ws);
+    const int part = lane & 15;                                     // 16-byte piece of the 256-byte row this lane copies
+    const size_t part_off = (part < 8) ? (size_t)part * 8 : (size_t)d + (size_t)(part - 8) * 8;
+
+    for (int sb = 0; sb < nv; sb += AM_STAGE) {
+        // ---- virtual positions sb + 32*hv + lane: row index and meta = owner mask (bits 0-3) | masked-source (bit 4) ----
+        int rowidx[2], meta[2];
+#pragma unroll
+        for (int hv = 0; hv < 2; ++hv) {
+            rowidx[hv] = -1; meta[hv] = 0;
+            const int v = sb + 32 * hv + lane;
             if (v < nv) {
                 if (SELF) {
-                    if (v < cshared) { rowidx = (b * a.beam + anc0[v]) * a.T_max + v; meta = 0xF; }
+                    if (v < cshared) { rowidx[hv] = (b * a.beam + anc0[v]) * a.T_max + v; meta[hv] = 0xF; }
                     else {
                         const int vt = v - cshared;
                         const int qi = (vt >= tl) + (vt >= 2 * tl) + (vt >= 3 * tl);
                         const int p = cshared + vt - qi * tl;
                         const int slot = (p == n - 1) ? (q0 + qi) : anc0[(size_t)qi * a.T_max + p];
-                        rowidx = (b * a.beam + slot) * a.T_max + p;
-                        meta = 1 << qi;
+                        rowidx[hv] = (b * a.beam + slot) * a.T_max + p;
+                        meta[hv] = 1 << qi;
                     }
                 } else {
-                    rowidx = v;
-                    meta = 0xF | ((mrow != nullptr && mrow[v] == 0) ? 0x10 : 0);
+                    rowidx[hv] = v;
+                    meta[hv] = 0xF | ((mrow != nullptr && mrow[v] == 0) ? 0x10 : 0);
                 }
             }
         }
-        // ---- S = Q.K^T for 4 tiles of 8 positions ----
-        uint4 kr[4][2];
+        const int nchunk = (nv - sb > 32) ? 2 : 1;                   // 32-position chunks in this stage (warp-uniform)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int r = __shfl_sync(0xffffffffu, rowidx, 8 * j + nl);
-            kr[j][0] = make_uint4(0u, 0u, 0u, 0u); kr[j][1] = make_uint4(0u, 0u, 0u, 0u);
-            if (r >= 0) {
-                const uint4* kp = reinterpret_cast<const uint4*>(base + (size_t)r * pos_stride + 16 * c);
-                kr[j][0] = kp[0]; kr[j][1] = kp[1];
+        for (int k = 0; k < AM_STAGE / 2; ++k) {
+            if (k < 16 * nchunk) {
+                const int row = 2 * k + (lane >> 4);
+                const int r = __shfl_sync(0xffffffffu, rowidx[k >> 4], row & 31);
+                const T* src = base + ((r >= 0) ? (size_t)r * pos_stride + part_off : (size_t)0);
+                const uint32_t dst = ws_u32 + row * AM_ROWB + part * 16;
+                const int nbytes = (r >= 0) ? 16 : 0;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nbytes) : "memory");
             }
         }
-        float s[4][4];
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncwarp();
+
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            s[j][0] = 0.f; s[j][1] = 0.f; s[j][2] = 0.f; s[j][3] = 0.f;
-            const uint32_t kw[8] = {kr[j][0].x, kr[j][0].y, kr[j][0].z, kr[j][0].w, kr[j][1].x, kr[j][1].y, kr[j][1].z, kr[j][1].w};
+        for (int cb = 0; cb < 2; ++cb) {
+            if (cb < nchunk) {
+                const unsigned char* wc = ws + cb * 32 * AM_ROWB;
+                // ---- S = Q.K^T for 4 tiles of 8 positions ----
+                float s[4][4];
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) {
-                const uint32_t ah[4] = {qhi[2 * ks], 0u, qhi[2 * ks + 1], 0u};
-                const uint32_t al[4] = {qlo[2 * ks], 0u, qlo[2 * ks + 1], 0u};
-                Mma16<T>::mma(s[j], ah, kw[2 * ks], kw[2 * ks + 1]);
-                Mma16<T>::mma(s[j], al, kw[2 * ks], kw[2 * ks + 1]);
+                for (int j = 0; j < 4; ++j) {
+                    s[j][0] = 0.f; s[j][1] = 0.f; s[j][2] = 0.f; s[j][3] = 0.f;
+                    const uint4* kp = reinterpret_cast<const uint4*>(wc + (8 * j + nl) * AM_ROWB + 32 * c);
+                    const uint4 k0 = kp[0], k1 = kp[1];
+                    const uint32_t kw[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint32_t ah[4] = {qhi[2 * ks], 0u, qhi[2 * ks + 1], 0u};
+                        const uint32_t al[4] = {qlo[2 * ks], 0u, qlo[2 * ks + 1], 0u};
+                        Mma16<T>::mma(s[j], ah, kw[2 * ks], kw[2 * ks + 1]);
+                        Mma16<T>::mma(s[j], al, kw[2 * ks], kw[2 * ks + 1]);
+                    }
+                }
+                // ---- mask, online softmax on the C fragments (row qrow, positions 8j + 2c + {0,1} of the chunk) ----
+                float mc = -INFINITY;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int mt = __shfl_sync(0xffffffffu, meta[cb], 8 * j + 2 * c + e);
+                        float x = s[j][e];
+                        if (mt & 0x10) x += -10000.0f;       // additive mask (1 - m) * -10000: reference src/bert_seq2seq.py:36-37
+                        x = ((mt >> qrow) & 1) ? x : -INFINITY;
+                        s[j][e] = x;
+                        mc = fmaxf(mc, x);
+                    }
+                mc = fmaxf(mc, __shfl_xor_sync(0xffffffffu, mc, 1));
+                mc = fmaxf(mc, __shfl_xor_sync(0xffffffffu, mc, 2));
+                const float m_new = fmaxf(m_run, mc);
+                const float m_use = (m_new == -INFINITY) ? 0.f : m_new;  // nothing visible yet for this row: all p = 0
+                const float corr = __expf(m_run - m_use);                // m_run = -inf -> 0
+                m_run = m_new;
+                float psum = 0.f;
+                uint32_t phi[2][4], plo[2][4];
+#pragma unroll
+                for (int t = 0; t < 2; ++t) {
+                    const float p0 = __expf(s[2 * t][0] - m_use), p1 = __expf(s[2 * t][1] - m_use);
+                    const float p2 = __expf(s[2 * t + 1][0] - m_use), p3 = __expf(s[2 * t + 1][1] - m_use);
+                    psum += (p0 + p1) + (p2 + p3);
+                    split2<T>(p0, p1, phi[t][0], plo[t][0]);
+                    split2<T>(p2, p3, phi[t][2], plo[t][2]);
+                    phi[t][1] = 0u; phi[t][3] = 0u; plo[t][1] = 0u; plo[t][3] = 0u;
+                }
+                l_run = l_run * corr + psum;
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= corr; o[nt][1] *= corr; }
+                // ---- O += P.V : rows 16t + {2c, 2c+1, 2c+8, 2c+9}, dims [8nl, 8nl+8) ----
+#pragma unroll
+                for (int t = 0; t < 2; ++t) {
+                    const unsigned char* vp = wc + (16 * t + 2 * c) * AM_ROWB + 128 + 16 * nl;
+                    const uint4 v0 = *reinterpret_cast<const uint4*>(vp), v1 = *reinterpret_cast<const uint4*>(vp + AM_ROWB);
+                    const uint4 v2 = *reinterpret_cast<const uint4*>(vp + 8 * AM_ROWB), v3 = *reinterpret_cast<const uint4*>(vp + 9 * AM_ROWB);
+                    const uint32_t va[4] = {v0.x, v0.y, v0.z, v0.w}, vb_[4] = {v1.x, v1.y, v1.z, v1.w};
+                    const uint32_t vc[4] = {v2.x, v2.y, v2.z, v2.w}, vd[4] = {v3.x, v3.y, v3.z, v3.w};
+#pragma unroll
+                    for (int nt = 0; nt < 8; ++nt) {
+                        const uint32_t sel = (nt & 1) ? 0x7632u : 0x5410u;
+                        const uint32_t b0 = __byte_perm(va[nt >> 1], vb_[nt >> 1], sel);
+                        const uint32_t b1 = __byte_perm(vc[nt >> 1], vd[nt >> 1], sel);
+                        Mma16<T>::mma(o[nt], phi[t], b0, b1);
+                        Mma16<T>::mma(o[nt], plo[t], b0, b1);
+                    }
+                }
             }
         }
-        // ---- V rows of this chunk (issued before the softmax arithmetic) ----
-        uint4 vr[2][4];
-#pragma unroll
-        for (int t = 0; t < 2; ++t)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int r = __shfl_sync(0xffffffffu, rowidx, 16 * t + 2 * c + (i & 1) + 8 * (i >> 1));
-                vr[t][i] = make_uint4(0u, 0u, 0u, 0u);
-                if (r >= 0) vr[t][i] = *reinterpret_cast<const uint4*>(base + (size_t)r * pos_stride + d + 8 * nl);
-            }
-        // ---- mask, online softmax on the C fragments (row qrow, positions vb + 8j + 2c + {0,1}) ----
-        float mc = -INFINITY;
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int mt = __shfl_sync(0xffffffffu, meta, 8 * j + 2 * c + e);
-                float x = s[j][e];
-                if (mt & 0x10) x += -10000.0f;               // additive mask (1 - m) * -10000: reference src/bert_seq2seq.py:36-37
-                x = ((mt >> qrow) & 1) ? x : -INFINITY;
-                s[j][e] = x;
-                mc = fmaxf(mc, x);
-            }
-        mc = fmaxf(mc, __shfl_xor_sync(0xffffffffu, mc, 1));
-        mc = fmaxf(mc, __shfl_xor_sync(0xffffffffu, mc, 2));
-        const float m_new = fmaxf(m_run, mc);
-        const float m_use = (m_new == -INFINITY) ? 0.f : m_new;          // nothing visible yet for this row: all p = 0
-        const float corr = __expf(m_run - m_use);                        // m_run = -inf -> 0
-        m_run = m_new;
-        float psum = 0.f;
-        uint32_t phi[2][4], plo[2][4];
-#pragma unroll
-        for (int t = 0; t < 2; ++t) {
-            const float p0 = __expf(s[2 * t][0] - m_use), p1 = __expf(s[2 * t][1] - m_use);
-            const float p2 = __expf(s[2 * t + 1][0] - m_use), p3 = __expf(s[2 * t + 1][1] - m_use);
-            psum += (p0 + p1) + (p2 + p3);
-            split2<T>(p0, p1, phi[t][0], plo[t][0]);
-            split2<T>(p2, p3, phi[t][2], plo[t][2]);
-            phi[t][1] = 0u; phi[t][3] = 0u; plo[t][1] = 0u; plo[t][3] = 0u;
-        }
-        l_run = l_run * corr + psum;
-#pragma unroll
-        for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= corr; o[nt][1] *= corr; }
-        // ---- O += P.V ----
-#pragma unroll
-        for (int t = 0; t < 2; ++t) {
-            const uint32_t va[4] = {vr[t][0].x, vr[t][0].y, vr[t][0].z, vr[t][0].w};
-            const uint32_t vb_[4] = {vr[t][1].x, vr[t][1].y, vr[t][1].z, vr[t][1].w};
-            const uint32_t vc[4] = {vr[t][2].x, vr[t][2].y, vr[t][2].z, vr[t][2].w};
-            const uint32_t vd[4] = {vr[t][3].x, vr[t][3].y, vr[t][3].z, vr[t][3].w};
-#pragma unroll
-            for (int nt = 0; nt < 8; ++nt) {
-                const uint32_t sel = (nt & 1) ? 0x7632u : 0x5410u;
-                const uint32_t b0 = __byte_perm(va[nt >> 1], vb_[nt >> 1], sel);
-                const uint32_t b1 = __byte_perm(vc[nt >> 1], vd[nt >> 1], sel);
-                Mma16<T>::mma(o[nt], phi[t], b0, b1);
-                Mma16<T>::mma(o[nt], plo[t], b0, b1);
-            }
-        }
+        __syncwarp();                    // the stage buffer is rewritten by the next iteration
     }
     // ---- normalise and store: lane (nl < nq, c) holds dims [16c,16c+16) of row nl ----
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
@@ -289,8 +315,15 @@ static int launch_attn_mma(AttnMmaArgs a, bool self, cudaStream_t s) {
     const int B = a.M / a.beam, H = a.d / DH;
     a.n_warps = B * H * ((a.beam + 3) / 4);
     const dim3 grid((a.n_warps + AM_WARPS - 1) / AM_WARPS), block(AM_THREADS);
-    cudaError_t e = self ? itb_launch(attn_mma_kernel<T, true>, grid, block, (size_t)0, s, a)
-                         : itb_launch(attn_mma_kernel<T, false>, grid, block, (size_t)0, s, a);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e1 = cudaFuncSetAttribute(attn_mma_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AM_SMEM);
+        cudaError_t e2 = cudaFuncSetAttribute(attn_mma_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AM_SMEM);
+        if (e1 != cudaSuccess || e2 != cudaSuccess) { itb_set_error("attention: cudaFuncSetAttribute failed"); return -1; }
+        attr_set = true;
+    }
+    cudaError_t e = self ? itb_launch(attn_mma_kernel<T, true>, grid, block, (size_t)AM_SMEM, s, a)
+                         : itb_launch(attn_mma_kernel<T, false>, grid, block, (size_t)AM_SMEM, s, a);
     if (e != cudaSuccess) { itb_set_error("%s: launch failed: %s", self ? "self_attention" : "cross_attention", cudaGetErrorString(e)); return -1; }
     return itb_check_launch(self ? "self_attention" : "cross_attention");
 }
