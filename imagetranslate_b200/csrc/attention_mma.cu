@@ -106,16 +106,19 @@ __global__ void __launch_bounds__(AM_THREADS, 3) attn_mma_kernel(AttnMmaArgs a) 
     if (c4.y != 0 || sdone != 0) return;
     if (SELF) n = c4.x;                                  // self: positions 0..step-1
 
-    // ---- Q fragments: row nl (< nq) of the A operand, dims [16c,16c+16) in k-slice order, scaled by 1/8, hi + lo ----
-    uint32_t qhi[8], qlo[8];
+    // ---- Q fragments.  A-operand quad of k-slice ks = {a0: row nl, k 0-7 | a1: row nl+8, k 0-7 | a2: row nl, k 8-15 |
+    //      a3: row nl+8, k 8-15}.  Rows 0..3 carry the hi 16-bit part of the 4 queries and rows 8..11 the lo part, so ONE
+    //      mma yields hi.K in c0,c1 and lo.K in c2,c3 (no wasted accumulator rows, no zero registers).  Dims [16c,16c+16)
+    //      of the query in k-slice order, scaled by 1/8 (exact). ----
+    uint32_t aq[4][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        split2<T>(qx[i].x * 0.125f, qx[i].y * 0.125f, qhi[2 * i], qlo[2 * i]);
-        split2<T>(qx[i].z * 0.125f, qx[i].w * 0.125f, qhi[2 * i + 1], qlo[2 * i + 1]);
+        split2<T>(qx[i].x * 0.125f, qx[i].y * 0.125f, aq[i][0], aq[i][1]);
+        split2<T>(qx[i].z * 0.125f, qx[i].w * 0.125f, aq[i][2], aq[i][3]);
     }
     if (nl >= nq) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) { qhi[i] = 0u; qlo[i] = 0u; }
+        for (int i = 0; i < 4; ++i) { aq[i][0] = 0u; aq[i][1] = 0u; aq[i][2] = 0u; aq[i][3] = 0u; }
     }
 
     // ---- geometry of the virtual position list ----
@@ -232,12 +235,9 @@ __global__ void __launch_bounds__(AM_THREADS, 3) attn_mma_kernel(AttnMmaArgs a) 
                     const uint4 k0 = kp[0], k1 = kp[1];
                     const uint32_t kw[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {
-                        const uint32_t ah[4] = {qhi[2 * ks], 0u, qhi[2 * ks + 1], 0u};
-                        const uint32_t al[4] = {qlo[2 * ks], 0u, qlo[2 * ks + 1], 0u};
-                        Mma16<T>::mma(s[j], ah, kw[2 * ks], kw[2 * ks + 1]);
-                        Mma16<T>::mma(s[j], al, kw[2 * ks], kw[2 * ks + 1]);
-                    }
+                    for (int ks = 0; ks < 4; ++ks) Mma16<T>::mma(s[j], aq[ks], kw[2 * ks], kw[2 * ks + 1]);
+                    s[j][0] += s[j][2];                      // hi.K (rows 0..3) + lo.K (rows 8..11)
+                    s[j][1] += s[j][3];
                 }
                 // ---- mask, online softmax on the C fragments (row qrow, positions 8j + 2c + {0,1} of the chunk) ----
                 float mc = -INFINITY;
@@ -259,19 +259,20 @@ __global__ void __launch_bounds__(AM_THREADS, 3) attn_mma_kernel(AttnMmaArgs a) 
                 const float corr = __expf(m_run - m_use);                // m_run = -inf -> 0
                 m_run = m_new;
                 float psum = 0.f;
-                uint32_t phi[2][4], plo[2][4];
+                uint32_t ap[2][4];                           // P as A quads: hi in rows 0..3, lo in rows 8..11 (as for Q)
 #pragma unroll
                 for (int t = 0; t < 2; ++t) {
                     const float p0 = __expf(s[2 * t][0] - m_use), p1 = __expf(s[2 * t][1] - m_use);
                     const float p2 = __expf(s[2 * t + 1][0] - m_use), p3 = __expf(s[2 * t + 1][1] - m_use);
                     psum += (p0 + p1) + (p2 + p3);
-                    split2<T>(p0, p1, phi[t][0], plo[t][0]);
-                    split2<T>(p2, p3, phi[t][2], plo[t][2]);
-                    phi[t][1] = 0u; phi[t][3] = 0u; plo[t][1] = 0u; plo[t][3] = 0u;
+                    split2<T>(p0, p1, ap[t][0], ap[t][1]);
+                    split2<T>(p2, p3, ap[t][2], ap[t][3]);
                 }
                 l_run = l_run * corr + psum;
+                if (corr != 1.0f) {
 #pragma unroll
-                for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= corr; o[nt][1] *= corr; }
+                    for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= corr; o[nt][1] *= corr; o[nt][2] *= corr; o[nt][3] *= corr; }
+                }
                 // ---- O += P.V : rows 16t + {2c, 2c+1, 2c+8, 2c+9}, dims [8nl, 8nl+8) ----
 #pragma unroll
                 for (int t = 0; t < 2; ++t) {
@@ -285,8 +286,7 @@ __global__ void __launch_bounds__(AM_THREADS, 3) attn_mma_kernel(AttnMmaArgs a) 
                         const uint32_t sel = (nt & 1) ? 0x7632u : 0x5410u;
                         const uint32_t b0 = __byte_perm(va[nt >> 1], vb_[nt >> 1], sel);
                         const uint32_t b1 = __byte_perm(vc[nt >> 1], vd[nt >> 1], sel);
-                        Mma16<T>::mma(o[nt], phi[t], b0, b1);
-                        Mma16<T>::mma(o[nt], plo[t], b0, b1);
+                        Mma16<T>::mma(o[nt], ap[t], b0, b1);
                     }
                 }
             }
@@ -301,8 +301,8 @@ __global__ void __launch_bounds__(AM_THREADS, 3) attn_mma_kernel(AttnMmaArgs a) 
         uint32_t w[8];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            w[i] = Mma16<T>::pack(o[2 * i][0] * inv, o[2 * i + 1][0] * inv);
-            w[4 + i] = Mma16<T>::pack(o[2 * i][1] * inv, o[2 * i + 1][1] * inv);
+            w[i] = Mma16<T>::pack((o[2 * i][0] + o[2 * i][2]) * inv, (o[2 * i + 1][0] + o[2 * i + 1][2]) * inv);
+            w[4 + i] = Mma16<T>::pack((o[2 * i][1] + o[2 * i][3]) * inv, (o[2 * i + 1][1] + o[2 * i + 1][3]) * inv);
         }
         uint4* dp = reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.ctx) + (size_t)(row0 + nl) * d + hoff + 16 * c);
         dp[0] = make_uint4(w[0], w[1], w[2], w[3]);
