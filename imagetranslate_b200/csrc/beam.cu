@@ -52,7 +52,8 @@ __device__ __forceinline__ void warp_select(float* val, int* idx, int n, int K, 
     }
 }
 
-template <int KT>
+// PRECISE: expf for the fp32 parity mode; otherwise EX2 with a pre-scaled argument (16-bit modes).
+template <int KT, bool PRECISE>
 __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     __shared__ float s_val[8 * KT > 16 * 16 ? 8 * KT : 16 * 16];   // phase 1: per-warp lists; phase 2: row candidates
     __shared__ int s_idx[8 * KT > 16 * 16 ? 8 * KT : 16 * 16];
@@ -89,16 +90,52 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
         float m = -INFINITY, s = 0.f;
         const int lo = c * a.chunk, hi = min(V, lo + a.chunk);
         const float* row = a.logits + (size_t)r * a.ldl;
-        for (int i = lo + tid * 4; i < hi; i += 256 * 4) {
-            float4 x4 = *reinterpret_cast<const float4*>(row + i);
-            float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+        // 4 float4 per thread in flight; per batch of 16 logits: one max tree, a (rare) rescale of the running sum, one
+        // FFMA + EX2 + FADD per element, and the top-K insertion only when the batch maximum beats the K-th best so far.
+        constexpr float kLog2e = 1.4426950408889634f;
+        // software pipeline: the 4 float4 of the NEXT batch are requested before the current batch is consumed
+        // (8 x 16 B in flight per thread)
+        const float4 kNegInf4 = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+        float4 nx[4];
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                float x = xs[e];
-                if (i + e < hi) {
-                    if (x > m) { s = s * expf(m - x) + 1.f; m = x; } else { s += expf(x - m); }
+        for (int u = 0; u < 4; ++u) {
+            const int i = lo + tid * 4 + u * 256 * 4;
+            nx[u] = (i < hi) ? __ldcs(reinterpret_cast<const float4*>(row + i)) : kNegInf4;
+        }
+        for (int i0 = lo + tid * 4; i0 < hi; i0 += 4 * 256 * 4) {
+            float xs[16];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * 256 * 4;
+                const float4 x4 = nx[u];
+                xs[4 * u] = x4.x;
+                xs[4 * u + 1] = (i + 1 < hi) ? x4.y : -INFINITY;
+                xs[4 * u + 2] = (i + 2 < hi) ? x4.z : -INFINITY;
+                xs[4 * u + 3] = (i + 3 < hi) ? x4.w : -INFINITY;
+                const int in = i + 4 * 256 * 4;
+                nx[u] = (in < hi) ? __ldcs(reinterpret_cast<const float4*>(row + in)) : kNegInf4;
+            }
+            float bm = xs[0];
+#pragma unroll
+            for (int e = 1; e < 16; ++e) bm = fmaxf(bm, xs[e]);
+            if (bm > m) {                                                               // rare once the maximum settled
+                s = (m == -INFINITY) ? 0.f : s * (PRECISE ? expf(m - bm) : exp2f((m - bm) * kLog2e));
+                m = bm;
+            }
+            if (PRECISE) {
+#pragma unroll
+                for (int e = 0; e < 16; ++e) s += expf(xs[e] - m);                      // exp(-inf) = 0 for the padding
+            } else {
+                const float nm = -m * kLog2e;
+#pragma unroll
+                for (int e = 0; e < 16; ++e) s += exp2f(fmaf(xs[e], kLog2e, nm));
+            }
+            if (bm > v[KT - 1]) {
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                    const float x = xs[e];
                     if (x > v[KT - 1]) {
-                        v[KT - 1] = x; id[KT - 1] = i + e;
+                        v[KT - 1] = x; id[KT - 1] = i0 + (e >> 2) * 256 * 4 + (e & 3);
 #pragma unroll
                         for (int j = KT - 1; j > 0; --j) {
                             if (v[j] > v[j - 1]) {
@@ -306,10 +343,14 @@ int itb_beam_step(const itb_config* c, void* stream) {
     dim3 grid(c->n_chunk, c->B * c->beam);
     cudaStream_t s = (cudaStream_t)stream;
     cudaError_t e;
+    const bool precise = (c->dtype == ITB_F32);
     switch (kt_for(c->beam)) {
-        case 4: e = itb_launch(beam_step_kernel<4>, grid, dim3(256), (size_t)0, s, a); break;
-        case 8: e = itb_launch(beam_step_kernel<8>, grid, dim3(256), (size_t)0, s, a); break;
-        default: e = itb_launch(beam_step_kernel<16>, grid, dim3(256), (size_t)0, s, a); break;
+        case 4: e = precise ? itb_launch(beam_step_kernel<4, true>, grid, dim3(256), (size_t)0, s, a)
+                            : itb_launch(beam_step_kernel<4, false>, grid, dim3(256), (size_t)0, s, a); break;
+        case 8: e = precise ? itb_launch(beam_step_kernel<8, true>, grid, dim3(256), (size_t)0, s, a)
+                            : itb_launch(beam_step_kernel<8, false>, grid, dim3(256), (size_t)0, s, a); break;
+        default: e = precise ? itb_launch(beam_step_kernel<16, true>, grid, dim3(256), (size_t)0, s, a)
+                             : itb_launch(beam_step_kernel<16, false>, grid, dim3(256), (size_t)0, s, a); break;
     }
     if (e != cudaSuccess) { itb_set_error("beam_step: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("beam_step");

@@ -319,10 +319,12 @@ static int num_sms() {
     return n;
 }
 
-// Tile plan.  The decode GEMMs are weight-streaming and latency-bound, so the activation rows per tile (UMMA N = mt)
-// and the split-K factor are chosen to spread the weight matrix over as many SMs as possible:
-//   cost = waves * (k-blocks per tile * bytes staged per k-block + a fixed per-tile overhead).
-// Split-K (partials summed by the consumer in a fixed order -> deterministic) only when the caller allows it.
+// Tile plan.  The decode GEMMs are weight-streaming and latency-bound at small M, so the activation rows per tile
+// (UMMA N = mt) and the split-K factor are chosen to spread the weight matrix over as many SMs as possible:
+//   cost = waves * (bytes staged per tile + bytes of the fp32 output tile written and re-read by the consumer + fixed).
+// Every split-K partial is a full fp32 output written by the GEMM and summed in add_ln, so at large M (where an
+// unsplit launch already fills most SMs) the output term makes split-K lose.  Split-K (partials summed by the
+// consumer in a fixed order -> deterministic) only when the caller allows it.
 void itb_tc_plan(int M, int N, int K, int max_split, int* mt_out, int* split_out) {
     const int n_tiles = (N + TC_BN - 1) / TC_BN, KB = K / TC_BK;
     long best_cost = -1;
@@ -332,7 +334,10 @@ void itb_tc_plan(int M, int N, int K, int max_split, int* mt_out, int* split_out
             if (KB % sp != 0) continue;
             const long tiles = (long)n_tiles * ((M + mt - 1) / mt) * sp;
             const long waves = (tiles + num_sms() - 1) / num_sms();
-            const long cost = waves * ((long)(KB / sp) * (TC_BN + mt) + 6 * 160);
+            const int rows = mt < M ? mt : M;                                // real activation rows in a tile
+            const long staged = (long)(KB / sp) * (TC_BN + mt) * (TC_BK * 2);
+            const long outb = (long)TC_BN * rows * 8;                          // fp32 write + re-read
+            const long cost = waves * (staged + outb + 6 * 160 * 128);
             if (best_cost < 0 || cost < best_cost) { *mt_out = mt; *split_out = sp; best_cost = cost; }
         }
         if (mt >= M) break;
