@@ -35,7 +35,7 @@ def parse():
     ap.add_argument("--batch", type=int, default=4000)
     ap.add_argument("--capacity", type=int, default=600)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp16", "fp32"])
-    ap.add_argument("--rows", type=int, default=1024, help="beam rows per super-batch (consecutive reference batches decoded in lockstep)")
+    ap.add_argument("--rows", type=int, default=4096, help="beam rows per super-batch (consecutive reference batches decoded in lockstep)")
     ap.add_argument("--lanes", type=int, default=2, help="batches in flight per GPU (separate streams; results do not depend on it)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sentences", type=int, default=6)

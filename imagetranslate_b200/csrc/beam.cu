@@ -26,6 +26,12 @@ struct BeamArgs {
     float* cand_val; int* cand_idx; float* chunk_max; float* chunk_sum; int* sent_counter;
 };
 
+__device__ __forceinline__ float fast_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 __device__ __forceinline__ bool better(float v, int i, float bv, int bi) { return v > bv || (v == bv && i < bi); }
 
 // One warp selects the top-K of (val, idx)[0..n) in shared memory by (val desc, idx asc).
@@ -84,9 +90,11 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     const bool skip = gdone || row_zero || (first && kslot != 0);            // step 1 has one row per sentence (:146,221)
 
     if (!skip) {
-        float v[KT]; int id[KT];
-#pragma unroll
-        for (int j = 0; j < KT; ++j) { v[j] = -INFINITY; id[j] = INT_MAX; }
+        // The warp keeps ONE sorted top-KT list, entry j in lane j (by value desc, index asc), and a warp-uniform
+        // threshold thr = its KT-th value: a logit is looked at again only when it reaches thr, which happens
+        // ~KT*ln(n/KT) times per warp over n logits instead of per thread.
+        float lv = -INFINITY; int li = INT_MAX;
+        float thr = -INFINITY;
         float m = -INFINITY, s = 0.f;
         const int lo = c * a.chunk, hi = min(V, lo + a.chunk);
         const float* row = a.logits + (size_t)r * a.ldl;
@@ -102,16 +110,20 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
             const int i = lo + tid * 4 + u * 256 * 4;
             nx[u] = (i < hi) ? __ldcs(reinterpret_cast<const float4*>(row + i)) : kNegInf4;
         }
-        for (int i0 = lo + tid * 4; i0 < hi; i0 += 4 * 256 * 4) {
+        // the loop bound is warp-uniform (the body holds warp collectives); lanes past `hi` carry -inf
+        for (int iw = lo + w * 128; iw < hi; iw += 4 * 256 * 4) {
+            const int i0 = iw + lane * 4;
             float xs[16];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int i = i0 + u * 256 * 4;
-                const float4 x4 = nx[u];
-                xs[4 * u] = x4.x;
-                xs[4 * u + 1] = (i + 1 < hi) ? x4.y : -INFINITY;
-                xs[4 * u + 2] = (i + 2 < hi) ? x4.z : -INFINITY;
-                xs[4 * u + 3] = (i + 3 < hi) ? x4.w : -INFINITY;
+                float4 x4 = nx[u];
+                if (i + 4 > hi && i < hi) {                  // ragged end of the chunk (V not a multiple of 4)
+                    if (i + 1 >= hi) x4.y = -INFINITY;
+                    if (i + 2 >= hi) x4.z = -INFINITY;
+                    if (i + 3 >= hi) x4.w = -INFINITY;
+                }
+                xs[4 * u] = x4.x; xs[4 * u + 1] = x4.y; xs[4 * u + 2] = x4.z; xs[4 * u + 3] = x4.w;
                 const int in = i + 4 * 256 * 4;
                 nx[u] = (in < hi) ? __ldcs(reinterpret_cast<const float4*>(row + in)) : kNegInf4;
             }
@@ -119,30 +131,37 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
 #pragma unroll
             for (int e = 1; e < 16; ++e) bm = fmaxf(bm, xs[e]);
             if (bm > m) {                                                               // rare once the maximum settled
-                s = (m == -INFINITY) ? 0.f : s * (PRECISE ? expf(m - bm) : exp2f((m - bm) * kLog2e));
+                s = (m == -INFINITY) ? 0.f : s * (PRECISE ? expf(m - bm) : fast_ex2((m - bm) * kLog2e));
                 m = bm;
             }
+            const float mref = (m == -INFINITY) ? 0.f : m;                              // lane entirely past `hi`: all terms are 0
             if (PRECISE) {
 #pragma unroll
-                for (int e = 0; e < 16; ++e) s += expf(xs[e] - m);                      // exp(-inf) = 0 for the padding
+                for (int e = 0; e < 16; ++e) s += expf(xs[e] - mref);                   // exp(-inf) = 0 for the padding
             } else {
-                const float nm = -m * kLog2e;
+                const float nm = -mref * kLog2e;
 #pragma unroll
-                for (int e = 0; e < 16; ++e) s += exp2f(fmaf(xs[e], kLog2e, nm));
+                for (int e = 0; e < 16; ++e) s += fast_ex2(fmaf(xs[e], kLog2e, nm));
             }
-            if (bm > v[KT - 1]) {
+            if (__any_sync(0xffffffffu, bm >= thr && bm > -INFINITY)) {
 #pragma unroll
                 for (int e = 0; e < 16; ++e) {
-                    const float x = xs[e];
-                    if (x > v[KT - 1]) {
-                        v[KT - 1] = x; id[KT - 1] = i0 + (e >> 2) * 256 * 4 + (e & 3);
-#pragma unroll
-                        for (int j = KT - 1; j > 0; --j) {
-                            if (v[j] > v[j - 1]) {
-                                float tv = v[j]; v[j] = v[j - 1]; v[j - 1] = tv;
-                                int ti = id[j]; id[j] = id[j - 1]; id[j - 1] = ti;
-                            }
+                    unsigned q = __ballot_sync(0xffffffffu, xs[e] >= thr && xs[e] > -INFINITY);
+                    while (q != 0u) {
+                        const int src = __ffs(q) - 1;
+                        q &= q - 1;
+                        const float x = __shfl_sync(0xffffffffu, xs[e], src);
+                        const int xi = i0 + (src - lane) * 4 + (e >> 2) * 256 * 4 + (e & 3);     // index of lane src's element e
+                        // sorted insert: entries better than (x, xi) form a prefix of the list
+                        const unsigned bet = __ballot_sync(0xffffffffu, better(lv, li, x, xi)) & ((1u << KT) - 1u);
+                        const int pos = __popc(bet);
+                        const float uv = __shfl_up_sync(0xffffffffu, lv, 1);
+                        const int ui = __shfl_up_sync(0xffffffffu, li, 1);
+                        if (lane < KT) {
+                            if (lane == pos) { lv = x; li = xi; }
+                            else if (lane > pos) { lv = uv; li = ui; }
                         }
+                        thr = __shfl_sync(0xffffffffu, lv, KT - 1);
                     }
                 }
             }
@@ -155,22 +174,8 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
             if (nm == -INFINITY) { s = 0.f; } else { s = s * expf(m - nm) + os * expf(om - nm); }
             m = nm;
         }
-        // warp-shuffle top-K merge: K rounds of "best head wins, owner pops"
-        for (int k = 0; k < K; ++k) {
-            float bv = v[0]; int bi = id[0];
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-                int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-                if (better(ov, oi, bv, bi)) { bv = ov; bi = oi; }
-            }
-            if (bi == id[0] && bi != INT_MAX) {
-#pragma unroll
-                for (int j = 0; j < KT - 1; ++j) { v[j] = v[j + 1]; id[j] = id[j + 1]; }
-                v[KT - 1] = -INFINITY; id[KT - 1] = INT_MAX;
-            }
-            if (lane == 0) { s_val[w * KT + k] = bv; s_idx[w * KT + k] = (bi == INT_MAX) ? -1 : bi; }
-        }
+        // the warp's list goes to shared memory as it is (lane k holds entry k)
+        if (lane < K) { s_val[w * KT + lane] = lv; s_idx[w * KT + lane] = (li == INT_MAX) ? -1 : li; }
         if (lane == 0) {
             for (int k = K; k < KT; ++k) { s_val[w * KT + k] = -INFINITY; s_idx[w * KT + k] = -1; }
             s_m[w] = m; s_s[w] = s;

@@ -56,7 +56,7 @@ __device__ __forceinline__ void ln_row_write(float4* v, int nv, int d, const flo
 }
 
 template <typename TA>
-__global__ void __launch_bounds__(32 * LN_ROWS) embed_ln_kernel(const ItbCtl* __restrict__ ctl, const int* __restrict__ tokens,
+__global__ void __launch_bounds__(32 * LN_ROWS, 4) embed_ln_kernel(const ItbCtl* __restrict__ ctl, const int* __restrict__ tokens,
                                                        const int* __restrict__ tgt_lang, const float* __restrict__ word,
                                                        const float* __restrict__ pos, const float* __restrict__ type,
                                                        const float* __restrict__ g, const float* __restrict__ b, float eps,
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(32 * LN_ROWS) embed_ln_kernel(const ItbCtl* __
 }
 
 template <typename TA>
-__global__ void __launch_bounds__(32 * LN_ROWS) add_ln_kernel(const ItbCtl* __restrict__ ctl, const float* __restrict__ y,
+__global__ void __launch_bounds__(32 * LN_ROWS, 4) add_ln_kernel(const ItbCtl* __restrict__ ctl, const float* __restrict__ y,
                                                      int n_partial, const float* __restrict__ g,
                                                      const float* __restrict__ b, float eps, float* __restrict__ x_f32,
                                                      TA* __restrict__ x_act, int M, int d) {

@@ -1,6 +1,6 @@
 #!/bin/bash
 # GPU check-in: parity tests, smoke, bench, launch list.  Usage: tools_gpu.sh [bench sentences]
-N=${1:-1024}
+N=${1:-4096}
 mkdir -p gpurun_out
 rm -f gpurun_out/summary.txt
 run() { name=$1; shift; timeout ${TMO:-300} "$@" > gpurun_out/$name.log 2>&1; echo "$name exit=$?" | tee -a gpurun_out/summary.txt; tail -n ${TAILN:-6} gpurun_out/$name.log; }
