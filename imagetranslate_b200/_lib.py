@@ -34,7 +34,7 @@ class Layer(C.Structure):
 class Config(C.Structure):
     _fields_ = (
         [(n, C.c_int) for n in ("dtype", "gemm_impl", "B", "beam", "d", "H", "F", "L", "V", "S", "T_max", "pad_id",
-                                "eos_id", "n_chunk", "reserved0")]
+                                "eos_id", "n_chunk", "fused_vocab")]
         + [("len_alpha", C.c_float), ("ln_eps", C.c_float)]
         + [(n, P) for n in ("emb_word", "emb_pos", "emb_type", "emb_ln_g", "emb_ln_b", "layers_host", "w_vocab",
                             "b_vocab", "tgt_lang", "max_lens", "sent_grp", "mem_len", "grp", "sent_done")]
@@ -48,6 +48,7 @@ _SIGS = {
     "itb_abi_version": (C.c_int, []),
     "itb_last_error": (C.c_char_p, []),
     "itb_topk_capacity": (C.c_int, [C.c_int]),
+    "itb_vocab_chunks": (C.c_int, [C.c_int]),
     "itb_sizeof_config": (C.c_int, []),
     "itb_sizeof_layer": (C.c_int, []),
     "itb_linear": (C.c_int, [C.c_int, C.c_int, C.c_int, P, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, P]),

@@ -14,6 +14,9 @@ int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const v
                 int M, int N, int K, int ldo, int act_f16, int mt, int nsplit, cudaStream_t s);
 int itb_make_tmap_16b(CUtensorMap* map, const void* base, int rows, int K, int box_rows, int is_f16);
 void itb_tc_plan(int M, int N, int K, int max_split, int* mt_out, int* split_out);
+int itb_gemm_tc_vocab(int kt, const CUtensorMap* tmX, const CUtensorMap* tmWv, const void* ctl, const float* bias, int rows, int V,
+                      int K, int act_f16, float* cand_val, int* cand_idx, float* chunk_max, float* chunk_sum, float* logits,
+                      int ldl, int n_chunk, cudaStream_t s);
 
 static thread_local char g_err[512] = "";
 
@@ -81,6 +84,8 @@ struct itb_decoder {
     std::vector<itb_layer> layers;
     std::vector<Linear> qkv, o, cq, co, f1, f2;
     Linear vocab;
+    bool vocab_fused = false;            // 16-bit modes: vocabulary GEMM with the softmax / top-k partials in its epilogue
+    CUtensorMap tm_vx, tm_vw;            // fused launch: activations [M][d] box 128, vocabulary weights [V][d] box 256
     cudaGraphExec_t exec = nullptr;      // `graph_steps` search steps captured once, replayed for the whole batch
     int graph_steps = 0;
     cudaStream_t cap_stream = nullptr;
@@ -92,6 +97,7 @@ int itb_abi_version(void) { return ITB_ABI_VERSION; }
 const char* itb_last_error(void) { return g_err; }
 int itb_sizeof_config(void) { return (int)sizeof(itb_config); }
 int itb_sizeof_layer(void) { return (int)sizeof(itb_layer); }
+int itb_vocab_chunks(int V) { return 2 * ((V + 255) / 256); }
 
 int itb_linear(int dtype, int impl, int epi, const void* A, const void* W, const float* bias, void* out, int M, int N,
                int K, int ldo, void* stream) {
@@ -133,7 +139,19 @@ int itb_decoder_create(const itb_config* c, itb_decoder** out) {
         Linear* ls[6] = {&d->qkv.back(), &d->o.back(), &d->cq.back(), &d->co.back(), &d->f1.back(), &d->f2.back()};
         for (int i = 0; i < 6 && r == 0; ++i) r = ls[i]->prepare(c->dtype, c->gemm_impl);
     }
-    if (r == 0) {
+    if (r == 0 && c->fused_vocab != 0) {
+        if (!use_tc(c->dtype, c->gemm_impl) || c->n_chunk != itb_vocab_chunks(c->V)) {
+            itb_set_error("decoder_create: fused_vocab needs a 16-bit tcgen05 decoder and n_chunk == itb_vocab_chunks(V)");
+            r = -2;
+        } else {
+            d->vocab_fused = true;
+            r = itb_make_tmap_16b(&d->tm_vx, c->x_act, M, D, 128, c->dtype == ITB_F16 ? 1 : 0);
+            if (r == 0) r = itb_make_tmap_16b(&d->tm_vw, c->w_vocab, c->V, D, 256, c->dtype == ITB_F16 ? 1 : 0);
+        }
+    } else if (r == 0 && c->logits == nullptr) {
+        itb_set_error("decoder_create: logits buffer missing");
+        r = -2;
+    } else if (r == 0) {
         d->vocab = make_linear(c->x_act, c->w_vocab, c->b_vocab, c->logits, M, c->V, D, ldl, ITB_EPI_BIAS_F32);
         r = d->vocab.prepare(c->dtype, c->gemm_impl);
     }
@@ -177,7 +195,11 @@ int itb_decoder_step(itb_decoder* dec, void* stream) {
         ITB_TRY(dec->f2[l].run(c.dtype, c.ctl, s));
         ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->f2[l].nsplit, w.ln3_g, w.ln3_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
     }
-    ITB_TRY(dec->vocab.run(c.dtype, c.ctl, s));
+    if (dec->vocab_fused)
+        ITB_TRY(itb_gemm_tc_vocab(itb_topk_capacity(c.beam), &dec->tm_vx, &dec->tm_vw, c.ctl, c.b_vocab, M, c.V, D, c.dtype == ITB_F16 ? 1 : 0,
+                                  c.cand_val, c.cand_idx, c.chunk_max, c.chunk_sum, c.logits, (c.V + 3) / 4 * 4, c.n_chunk, s));
+    else
+        ITB_TRY(dec->vocab.run(c.dtype, c.ctl, s));
     ITB_TRY(itb_beam_step(&c, stream));
     return 0;
 }

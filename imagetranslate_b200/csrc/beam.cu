@@ -24,6 +24,7 @@ struct BeamArgs {
     const int* max_lens;
     int* tokens; unsigned char* anc; float* scores; float* sizes; unsigned char* fin;
     float* cand_val; int* cand_idx; float* chunk_max; float* chunk_sum; int* sent_counter;
+    int fused;       // 1: phase 1 already ran inside the vocabulary GEMM epilogue (gemm_tc.cu); grid = one CTA per sentence
 };
 
 __device__ __forceinline__ float fast_ex2(float x) {
@@ -64,8 +65,6 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     __shared__ float s_val[8 * KT > 16 * 16 ? 8 * KT : 16 * 16];   // phase 1: per-warp lists; phase 2: row candidates
     __shared__ int s_idx[8 * KT > 16 * 16 ? 8 * KT : 16 * 16];
     __shared__ float s_m[8], s_s[8];
-    __shared__ float s_pool_val[8][32 * KT];                       // phase 2: chunk candidates of one row per warp
-    __shared__ int s_pool_idx[8][32 * KT];
     __shared__ float s_top_val[16];
     __shared__ int s_top_idx[16];
     __shared__ float s_rtop_val[8][16];
@@ -80,14 +79,15 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     const int step = ctl->step, cur = ctl->cur, nxt = cur ^ 1;
     const bool first = (step == 1);
     const int M = a.B * a.beam, K = a.beam, V = a.V;
-    const int c = blockIdx.x, r = blockIdx.y, b = r / a.beam, kslot = r % a.beam;
+    const bool fused = a.fused != 0;
+    const int c = blockIdx.x, r = fused ? blockIdx.y * a.beam : blockIdx.y, b = r / a.beam, kslot = r % a.beam;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
 
     const int gid = a.sent_grp[b];
     const bool gdone = a.sent_done[b] != 0;                                  // this sentence's reference batch has ended
     const bool lim = (!first) && (a.max_lens[b] < step + 1);                 // seq_gen.py:138
     const bool row_zero = (a.fin[(size_t)cur * M + r] != 0) || lim;          // :195-197
-    const bool skip = gdone || row_zero || (first && kslot != 0);            // step 1 has one row per sentence (:146,221)
+    const bool skip = fused || gdone || row_zero || (first && kslot != 0);            // step 1 has one row per sentence (:146,221)
 
     if (!skip) {
         // The warp keeps ONE sorted top-KT list, entry j in lane j (by value desc, index asc), and a warp-uniform
@@ -195,16 +195,18 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
         }
     }
 
-    // ---- ticket: the last CTA of this sentence runs phase 2 ----
-    __syncthreads();
-    if (tid == 0) {
-        __threadfence();
-        int t = atomicAdd(&a.sent_counter[b], 1);
-        s_last = (t == a.beam * a.n_chunk - 1);
-        if (s_last) __threadfence();
+    // ---- ticket: the last CTA of this sentence runs phase 2 (fused: every CTA is its sentence's only one) ----
+    if (!fused) {
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();
+            int t = atomicAdd(&a.sent_counter[b], 1);
+            s_last = (t == a.beam * a.n_chunk - 1);
+            if (s_last) __threadfence();
+        }
+        __syncthreads();
+        if (!s_last) return;
     }
-    __syncthreads();
-    if (!s_last) return;
 
     // ---------------------------------- phase 2 (one CTA per sentence) ----------------------------------
     if (!gdone) {
@@ -228,20 +230,53 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
                 rc_idx[kr * K + lane] = kr * V + lane;
             }
         } else {
-            const int n = a.n_chunk * KT;
-            float* pool_val = s_pool_val[w];
-            int* pool_idx = s_pool_idx[w];
-            for (int i = lane; i < n; i += 32) {
-                pool_val[i] = __ldcg(a.cand_val + (size_t)rr * n + i);
-                pool_idx[i] = __ldcg(a.cand_idx + (size_t)rr * n + i);
+            // log-sum-exp over the chunk partials, then a streaming top-K over the n_chunk * KT chunk candidates with the
+            // warp-level sorted list (entry j in lane j) and its threshold -- any number of chunks, no staging buffer
+            const int nc = a.n_chunk, n = nc * KT;
+            const float* cmp = a.chunk_max + (size_t)rr * nc;
+            const float* csp = a.chunk_sum + (size_t)rr * nc;
+            float mm = -INFINITY;
+            for (int ci = lane; ci < nc; ci += 32) mm = fmaxf(mm, __ldcg(cmp + ci));
+            mm = warp_max(mm);
+            float ss = 0.f;
+            for (int ci = lane; ci < nc; ci += 32) {
+                const float cm = __ldcg(cmp + ci);
+                if (cm != -INFINITY) ss += __ldcg(csp + ci) * expf(cm - mm);
             }
-            const float cm = (lane < a.n_chunk) ? __ldcg(a.chunk_max + (size_t)rr * a.n_chunk + lane) : -INFINITY;   // n_chunk <= 32
-            const float cs = (lane < a.n_chunk) ? __ldcg(a.chunk_sum + (size_t)rr * a.n_chunk + lane) : 0.f;
-            const float mm = warp_max(cm);
-            const float ss = warp_sum((cm != -INFINITY) ? cs * expf(cm - mm) : 0.f);
+            ss = warp_sum(ss);
             const float logz = logf(ss);
+            float lv = -INFINITY; int li = INT_MAX;
+            float thr = -INFINITY;
+            for (int i0 = 0; i0 < n; i0 += 32 * 8) {                    // 8 candidates per lane requested at once
+                float xv[8]; int xj[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int i = i0 + u * 32 + lane;
+                    xv[u] = -INFINITY; xj[u] = -1;
+                    if (i < n) { xv[u] = __ldcg(a.cand_val + (size_t)rr * n + i); xj[u] = __ldcg(a.cand_idx + (size_t)rr * n + i); }
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    unsigned q = __ballot_sync(0xffffffffu, xj[u] >= 0 && xv[u] >= thr && xv[u] > -INFINITY);
+                    while (q != 0u) {
+                        const int src = __ffs(q) - 1;
+                        q &= q - 1;
+                        const float cx = __shfl_sync(0xffffffffu, xv[u], src);
+                        const int cxi = __shfl_sync(0xffffffffu, xj[u], src);
+                        const unsigned bet = __ballot_sync(0xffffffffu, better(lv, li, cx, cxi)) & ((1u << KT) - 1u);
+                        const int pos = __popc(bet);
+                        const float uv = __shfl_up_sync(0xffffffffu, lv, 1);
+                        const int ui = __shfl_up_sync(0xffffffffu, li, 1);
+                        if (lane < KT) {
+                            if (lane == pos) { lv = cx; li = cxi; }
+                            else if (lane > pos) { lv = uv; li = ui; }
+                        }
+                        thr = __shfl_sync(0xffffffffu, lv, KT - 1);
+                    }
+                }
+            }
+            if (lane < K) { s_rtop_val[w][lane] = lv; s_rtop_idx[w][lane] = li; }
             __syncwarp();
-            warp_select(pool_val, pool_idx, n, K, s_rtop_val[w], s_rtop_idx[w], lane);
             if (lane < K) {
                 // log_softmax as ATen computes it: (x - max) - log(sum exp(x - max))   (seq_gen.py:194)
                 float lpz = (s_rtop_val[w][lane] - mm) - logz;
@@ -333,7 +368,7 @@ int itb_topk_capacity(int beam) { return kt_for(beam); }
 int itb_beam_step(const itb_config* c, void* stream) {
     ITB_REQUIRE(c->beam >= 1 && c->beam <= 16, "beam_step: beam width must be in [1,16]");
     ITB_REQUIRE(c->V >= c->beam, "beam_step: vocabulary smaller than the beam");
-    ITB_REQUIRE(c->n_chunk >= 1 && c->n_chunk <= 32, "beam_step: n_chunk must be in [1,32]");
+    ITB_REQUIRE(c->n_chunk >= 1 && (c->fused_vocab != 0 || c->n_chunk <= 32), "beam_step: n_chunk must be in [1,32]");
     BeamArgs a;
     a.ctl = reinterpret_cast<ItbCtl*>(c->ctl);
     a.grp = reinterpret_cast<ItbGrp*>(c->grp); a.sent_grp = c->sent_grp; a.sent_done = c->sent_done; a.G = c->G;
@@ -345,7 +380,8 @@ int itb_beam_step(const itb_config* c, void* stream) {
     a.max_lens = c->max_lens; a.tokens = c->tokens; a.anc = c->anc; a.scores = c->scores; a.sizes = c->sizes;
     a.fin = c->fin; a.cand_val = c->cand_val; a.cand_idx = c->cand_idx; a.chunk_max = c->chunk_max;
     a.chunk_sum = c->chunk_sum; a.sent_counter = c->sent_counter;
-    dim3 grid(c->n_chunk, c->B * c->beam);
+    a.fused = c->fused_vocab != 0 ? 1 : 0;
+    dim3 grid(a.fused ? 1 : c->n_chunk, a.fused ? c->B : c->B * c->beam);
     cudaStream_t s = (cudaStream_t)stream;
     cudaError_t e;
     const bool precise = (c->dtype == ITB_F32);

@@ -76,6 +76,11 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;
     return d;
 }
+__device__ __forceinline__ float tc_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -99,6 +104,125 @@ template <int MT> struct TcCfg {
     static constexpr int kTmemCols = (2 * MT) < 32 ? 32 : (2 * MT);            // power of two for MT in {32,64,128,256}
     static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 };
+
+// Tile t -> (split-K slice, tile of the MT-row operand, tile of the 128-row operand).  Normal launches walk the MT-row
+// (activation) tiles fastest so that concurrently running CTAs share one weight tile; the vocabulary launch (operands
+// swapped, see tc_epilogue_vocab) walks the 128-row (activation) tiles fastest for the same reason.
+template <bool SWAPPED>
+__device__ __forceinline__ void tc_tile_of(int t, int nsplit, int m_tiles, int n_tiles, int& ks, int& mt, int& nt) {
+    ks = t % nsplit;
+    const int u = t / nsplit;
+    if (SWAPPED) { nt = u % n_tiles; mt = u / n_tiles; }
+    else { mt = u % m_tiles; nt = u / m_tiles; }
+}
+
+// Output of the fused vocabulary projection (EPI >= ITB_EPI_VOCAB_K4): per (decoder row, chunk of 128 vocabulary
+// entries) the chunk's max logit, sum exp(logit - max) and top-KT (logit, index) -- what the beam kernel needs to finish
+// log_softmax + top-k (reference src/seq_gen.py:194,203) without an (M,V) logits tensor ever reaching HBM.
+struct TcVocabPart {
+    float* cand_val; int* cand_idx;      // [rows][n_chunk][KT]
+    float* chunk_max; float* chunk_sum;  // [rows][n_chunk]
+    float* logits; int ldl;              // optional full logits [rows][ldl] (parity traces); null in production
+    int n_chunk;
+};
+
+// Vocabulary launch: the operands are SWAPPED by the host -- the 128-row UMMA-A operand is the activation tile (TMEM lane
+// = decoder row) and the MT = 256 row UMMA-B operand is the weight tile (TMEM column = vocabulary entry) -- so each
+// epilogue thread owns ONE decoder row and walks its 128 logits of the tile in registers: + bias, running max / sum-exp
+// (EX2 with pre-scaled argument), sorted top-KT insertion (strict >, ascending index => lowest index wins ties).
+// Warps 4-7 take columns [0,128), warps 8-11 columns [128,256) of the tile; chunk index = 2 * vocab tile + half.
+template <int MT, int KT>
+__device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty, const float* __restrict__ bias,
+                                                  const TcVocabPart vp, int V, int rows, int total, int m_tiles, int n_tiles,
+                                                  int warp, int lane) {
+    static_assert(MT == 256, "the vocabulary epilogue is written for 256-entry tiles");
+    constexpr float kLog2e = 1.4426950408889634f;
+    const int q = warp & 3, half = (warp - 4) >> 2;
+    uint32_t as = 0, aphase = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        int ks, mt, nt;
+        tc_tile_of<true>(t, 1, m_tiles, n_tiles, ks, mt, nt);
+        mbar_wait(&tfull[as], aphase);
+        tc_fence_after();
+        const int r = nt * TC_BN + q * 32 + lane;                   // decoder row of this thread
+        const int vbase = mt * MT + half * 128;                     // first vocabulary entry of this warp's columns
+        if (nt * TC_BN + q * 32 < rows) {                           // warp-uniform: some row of this warp is real
+            float tv[KT]; int ti[KT];
+#pragma unroll
+            for (int j = 0; j < KT; ++j) { tv[j] = -INFINITY; ti[j] = -1; }
+            float m = -INFINITY, s = 0.f;
+#pragma unroll 1
+            for (int c0 = 0; c0 < 128; c0 += 32) {
+                const int v0 = vbase + c0;
+                if (v0 >= V) break;                                 // entries past V: the chunk stays (or ends) empty
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * MT + half * 128 + c0, v);
+                float x[32];
+                float bm = -INFINITY;
+                if (v0 + 32 <= V) {                                 // whole chunk inside the vocabulary: no per-entry checks
+                    const float4* bp = reinterpret_cast<const float4*>(bias + v0);       // same address in every lane
+#pragma unroll
+                    for (int j4 = 0; j4 < 8; ++j4) {
+                        const float4 b4 = __ldg(bp + j4);
+                        x[4 * j4] = __uint_as_float(v[4 * j4]) + b4.x;
+                        x[4 * j4 + 1] = __uint_as_float(v[4 * j4 + 1]) + b4.y;
+                        x[4 * j4 + 2] = __uint_as_float(v[4 * j4 + 2]) + b4.z;
+                        x[4 * j4 + 3] = __uint_as_float(v[4 * j4 + 3]) + b4.w;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) bm = fmaxf(bm, x[j]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const bool ok = v0 + j < V;
+                        x[j] = ok ? __uint_as_float(v[j]) + __ldg(bias + (ok ? v0 + j : 0)) : -INFINITY;
+                        bm = fmaxf(bm, x[j]);
+                    }
+                }
+                if (vp.logits != nullptr && r < rows) {
+                    float* lp = vp.logits + (size_t)r * vp.ldl + v0;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) if (v0 + j < V) lp[j] = x[j];
+                }
+                if (bm > m) {
+                    s = (m == -INFINITY) ? 0.f : s * tc_ex2((m - bm) * kLog2e);
+                    m = bm;
+                }
+                const float nm = -m * kLog2e;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) s += tc_ex2(fmaf(x[j], kLog2e, nm));       // padding: ex2(-inf) = 0
+                if (bm > tv[KT - 1]) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        if (x[j] > tv[KT - 1]) {
+                            tv[KT - 1] = x[j]; ti[KT - 1] = v0 + j;
+#pragma unroll
+                            for (int u = KT - 1; u > 0; --u) {
+                                if (tv[u] > tv[u - 1]) {
+                                    const float fv = tv[u]; tv[u] = tv[u - 1]; tv[u - 1] = fv;
+                                    const int fi = ti[u]; ti[u] = ti[u - 1]; ti[u - 1] = fi;
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            if (r < rows) {
+                const size_t ci = (size_t)r * vp.n_chunk + (size_t)(mt * 2 + half);
+                vp.chunk_max[ci] = m;
+                vp.chunk_sum[ci] = s;
+#pragma unroll
+                for (int j = 0; j < KT; j += 4) {
+                    *reinterpret_cast<float4*>(vp.cand_val + ci * KT + j) = make_float4(tv[j], tv[j + 1], tv[j + 2], tv[j + 3]);
+                    *reinterpret_cast<int4*>(vp.cand_idx + ci * KT + j) = make_int4(ti[j], ti[j + 1], ti[j + 2], ti[j + 3]);
+                }
+            }
+        }
+        tc_fence_before();
+        mbar_arrive(&tempty[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+}
 
 // Epilogue of warps 4-11: TMEM lane = weight row n (this lane), TMEM column = activation row m.  Per 32-column chunk one
 // tcgen05.ld, then 32 stores out[m][n] that are coalesced across the warp (consecutive n); the row pointer advances by
@@ -156,8 +280,9 @@ template <int MT, int EPI>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
                const ItbCtl* __restrict__ ctl, const float* __restrict__ bias, void* __restrict__ out, int M, int N,
-               int K, int ldo, int act_f16, int nsplit, size_t part_stride) {
+               int K, int ldo, int act_f16, int nsplit, size_t part_stride, const TcVocabPart vp) {
     using Cfg = TcCfg<MT>;
+    constexpr bool SWAPPED = (EPI >= ITB_EPI_VOCAB_K4);   // vocabulary launch: tmW = activations, tmA = weights
     extern __shared__ uint8_t smem_raw[];
     pdl_trigger();                                     // the next kernel of the chain may start its own prologue
 
@@ -198,11 +323,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
     // programmatic-dependency wait, so the HBM latency of the weight stream hides behind the predecessor's tail.
     int pre = 0;
     if (warp == 0 && lane == 0 && (int)blockIdx.x < total) {
-        const int t = blockIdx.x, ks = t % nsplit, nt = (t / nsplit) / m_tiles;
+        int ks, mt, nt;
+        tc_tile_of<SWAPPED>(blockIdx.x, nsplit, m_tiles, n_tiles, ks, mt, nt);
         pre = KB < Cfg::kStages ? KB : Cfg::kStages;
         for (int kb = 0; kb < pre; ++kb) {
             mbar_expect_tx(&full[kb], Cfg::kStageBytes);
-            tma_load_2d(smem_w + kb * (TC_BN * TC_BK * 2), &tmW, (ks * KB + kb) * TC_BK, nt * TC_BN, &full[kb]);
+            if (SWAPPED) tma_load_2d(smem_a + kb * (MT * TC_BK * 2), &tmA, (ks * KB + kb) * TC_BK, mt * MT, &full[kb]);
+            else tma_load_2d(smem_w + kb * (TC_BN * TC_BK * 2), &tmW, (ks * KB + kb) * TC_BK, nt * TC_BN, &full[kb]);
         }
     }
     pdl_wait();                                        // activations / ctl are valid from here on
@@ -211,9 +338,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
     if (warp == 0) {
         if (lane == 0) {
             if ((int)blockIdx.x < total) {
-                const int t = blockIdx.x, ks = t % nsplit, mt = (t / nsplit) % m_tiles;
-                for (int kb = 0; kb < pre; ++kb)
-                    tma_load_2d(smem_a + kb * (MT * TC_BK * 2), &tmA, (ks * KB + kb) * TC_BK, mt * MT, &full[kb]);
+                int ks, mt, nt;
+                tc_tile_of<SWAPPED>(blockIdx.x, nsplit, m_tiles, n_tiles, ks, mt, nt);
+                for (int kb = 0; kb < pre; ++kb) {
+                    if (SWAPPED) tma_load_2d(smem_w + kb * (TC_BN * TC_BK * 2), &tmW, (ks * KB + kb) * TC_BK, nt * TC_BN, &full[kb]);
+                    else tma_load_2d(smem_a + kb * (MT * TC_BK * 2), &tmA, (ks * KB + kb) * TC_BK, mt * MT, &full[kb]);
+                }
                 if (done)                              // search already terminated: drain the copies, then leave
                     for (int kb = 0; kb < pre; ++kb) mbar_wait(&full[kb], 0);
             }
@@ -221,7 +351,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
                 uint32_t stage = (pre == Cfg::kStages) ? 0 : pre, phase = (pre == Cfg::kStages) ? 1 : 0;
                 int kb0 = pre;
                 for (int t = blockIdx.x; t < total; t += gridDim.x) {
-                    const int ks = t % nsplit, mt = (t / nsplit) % m_tiles, nt = (t / nsplit) / m_tiles;
+                    int ks, mt, nt;
+                    tc_tile_of<SWAPPED>(t, nsplit, m_tiles, n_tiles, ks, mt, nt);
                     for (int kb = kb0; kb < KB; ++kb) {
                         mbar_wait(&empty[stage], phase ^ 1);
                         mbar_expect_tx(&full[stage], Cfg::kStageBytes);
@@ -261,7 +392,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
             }
         }
     } else if (warp >= 4) {
-        if (EPI == ITB_EPI_BIAS_F32) tc_epilogue<MT, EPI, float>(tmem_base, tfull, tempty, bias, reinterpret_cast<float*>(out), M, N, ldo, nsplit, part_stride, total, m_tiles, warp, lane);
+        if constexpr (EPI == ITB_EPI_VOCAB_K4) tc_epilogue_vocab<MT, 4>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane);
+        else if constexpr (EPI == ITB_EPI_VOCAB_K8) tc_epilogue_vocab<MT, 8>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane);
+        else if constexpr (EPI == ITB_EPI_VOCAB_K16) tc_epilogue_vocab<MT, 16>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane);
+        else if constexpr (EPI == ITB_EPI_BIAS_F32) tc_epilogue<MT, EPI, float>(tmem_base, tfull, tempty, bias, reinterpret_cast<float*>(out), M, N, ldo, nsplit, part_stride, total, m_tiles, warp, lane);
         else if (act_f16) tc_epilogue<MT, EPI, __half>(tmem_base, tfull, tempty, bias, reinterpret_cast<__half*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane);
         else tc_epilogue<MT, EPI, __nv_bfloat16>(tmem_base, tfull, tempty, bias, reinterpret_cast<__nv_bfloat16*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane);
     }
@@ -346,7 +480,7 @@ void itb_tc_plan(int M, int N, int K, int max_split, int* mt_out, int* split_out
 
 template <int MT, int EPI>
 static int launch_tc(const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCtl* ctl, const float* bias, void* out,
-                     int M, int N, int K, int ldo, int act_f16, int nsplit, cudaStream_t s) {
+                     int M, int N, int K, int ldo, int act_f16, int nsplit, cudaStream_t s, const TcVocabPart vp = TcVocabPart()) {
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<MT>::kSmemBytes);
@@ -356,7 +490,7 @@ static int launch_tc(const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCt
     const int total = ((N + TC_BN - 1) / TC_BN) * ((M + MT - 1) / MT) * nsplit;
     const int grid = total < num_sms() ? total : num_sms();
     cudaError_t e = itb_launch(gemm_tc_kernel<MT, EPI>, dim3(grid), dim3(TC_THREADS), (size_t)TcCfg<MT>::kSmemBytes, s, tmW, tmA,
-                               ctl, bias, out, M, N, K, ldo, act_f16, nsplit, (size_t)M * (size_t)ldo);
+                               ctl, bias, out, M, N, K, ldo, act_f16, nsplit, (size_t)M * (size_t)ldo, vp);
     if (e != cudaSuccess) { itb_set_error("gemm_tc: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("gemm_tc");
 }
@@ -383,4 +517,21 @@ int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const v
         case 256: return launch_tc_epi<256>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, nsplit, s);
         default: itb_set_error("linear(tcgen05): unsupported tile height %d", mt); return -2;
     }
+}
+
+// Fused vocabulary projection (operands swapped: tmX = activations [rows][K] box 128, tmWv = weights [V][K] box 256).
+// Writes per (row, 128-entry chunk) max / sum-exp / top-KT into vp; n_chunk must be itb_vocab_chunks(V).
+int itb_gemm_tc_vocab(int kt, const CUtensorMap* tmX, const CUtensorMap* tmWv, const void* ctl, const float* bias, int rows, int V,
+                      int K, int act_f16, float* cand_val, int* cand_idx, float* chunk_max, float* chunk_sum, float* logits,
+                      int ldl, int n_chunk, cudaStream_t s) {
+    ITB_REQUIRE(K % TC_BK == 0 && K >= TC_BK, "vocab(tcgen05): K must be a multiple of 64");
+    ITB_REQUIRE(n_chunk == 2 * ((V + 255) / 256), "vocab(tcgen05): n_chunk must be 2 * ceil(V / 256)");
+    TcVocabPart vp;
+    vp.cand_val = cand_val; vp.cand_idx = cand_idx; vp.chunk_max = chunk_max; vp.chunk_sum = chunk_sum;
+    vp.logits = logits; vp.ldl = ldl; vp.n_chunk = n_chunk;
+    const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
+    // kernel view: the 128-row operand ("N") is the activation matrix, the 256-row operand ("M") the weights
+    if (kt == 4) return launch_tc<256, ITB_EPI_VOCAB_K4>(*tmX, *tmWv, c, bias, nullptr, V, rows, K, 0, act_f16, 1, s, vp);
+    if (kt == 8) return launch_tc<256, ITB_EPI_VOCAB_K8>(*tmX, *tmWv, c, bias, nullptr, V, rows, K, 0, act_f16, 1, s, vp);
+    return launch_tc<256, ITB_EPI_VOCAB_K16>(*tmX, *tmWv, c, bias, nullptr, V, rows, K, 0, act_f16, 1, s, vp);
 }

@@ -157,15 +157,21 @@ class DecodeEngine(object):
             self._decoders[key] = dec
         return dec
 
-    def _config(self, pw, B, beam, S, T_max, pad, eos, alpha, G=1):
+    def _config(self, pw, B, beam, S, T_max, pad, eos, alpha, G=1, want_logits=False):
         ws, act, M = self.ws, _ACT[self.dtype_code], B * beam
         V4 = (pw.V + 3) // 4 * 4
-        n_chunk = max(1, min(32, -(-2368 // M), pw.V // 1024 if pw.V >= 1024 else 1))
+        # 16-bit tensor-core decoders: the vocabulary GEMM's epilogue emits the per-chunk max / sum-exp / top-K itself, no
+        # (M,V) logits tensor exists (it is only materialised for the parity traces of the tests)
+        fused = self.dtype_code != _lib.F32 and self.gemm_impl != _lib.GEMM_SIMT
+        if fused:
+            n_chunk = self.lib.itb_vocab_chunks(pw.V)
+        else:
+            n_chunk = max(1, min(32, -(-2368 // M), pw.V // 1024 if pw.V >= 1024 else 1))
         KT = self.lib.itb_topk_capacity(beam)
         c = _lib.Config()
         c.dtype, c.gemm_impl = self.dtype_code, self.gemm_impl
         c.B, c.beam, c.d, c.H, c.F, c.L, c.V, c.S, c.T_max = B, beam, pw.d, pw.H, pw.F, pw.L, pw.V, S, T_max
-        c.pad_id, c.eos_id, c.n_chunk, c.G = pad, eos, n_chunk, G
+        c.pad_id, c.eos_id, c.n_chunk, c.G, c.fused_vocab = pad, eos, n_chunk, G, int(fused)
         c.len_alpha, c.ln_eps = alpha, pw.ln_eps
         c.emb_word, c.emb_pos, c.emb_type = pw.emb_word.data_ptr(), pw.emb_pos.data_ptr(), pw.emb_type.data_ptr()
         c.emb_ln_g, c.emb_ln_b = pw.emb_ln_g.data_ptr(), pw.emb_ln_b.data_ptr()
@@ -182,11 +188,13 @@ class DecodeEngine(object):
             kv_self=ws.get("kv_self", pw.L * M * T_max * 2 * pw.d, act),
             x_f32=ws.get("x_f32", M * pw.d, f32), x_act=ws.get("x_act", M * pw.d, act), qkv=ws.get("qkv", M * 3 * pw.d, f32),
             ctx=ws.get("ctx", M * pw.d, act), y=ws.get("y", _lib.Y_PARTIALS * M * pw.d, f32), ffn_h=ws.get("ffn_h", M * pw.F, act),
-            logits=ws.get("logits", M * V4, f32), cand_val=ws.get("cand_val", M * n_chunk * KT, f32),
+            logits=ws.get("logits", M * V4 if (want_logits or not fused) else 1, f32), cand_val=ws.get("cand_val", M * n_chunk * KT, f32),
             cand_idx=ws.get("cand_idx", M * n_chunk * KT, i32), chunk_max=ws.get("chunk_max", M * n_chunk, f32),
             chunk_sum=ws.get("chunk_sum", M * n_chunk, f32), sent_counter=ws.get("sent_counter", B, i32))
         for k, v in t.items():
             setattr(c, k, v.data_ptr())
+        if fused and not want_logits:
+            c.logits = None
         t["out_tok"], t["out_len"] = ws.get("out_tok", B * T_max, i32), ws.get("out_len", 2 * B + 8, i32)
         t["first"], t["grp_max_len"] = ws.get("first", B, i32), ws.get("grp_max_len", G, i32)
         t["memory"] = ws.get("memory", B * S * pw.d, act)
@@ -216,7 +224,7 @@ class DecodeEngine(object):
         max_len = max(int(g["max_len"]) for g in groups)
         T_max = max(max_len, 2)
         has_mask = any(g["src_mask"] is not None for g in groups)
-        cfg, t = self._config(pw, B, beam, S, T_max, pad, eos, alpha, G)
+        cfg, t = self._config(pw, B, beam, S, T_max, pad, eos, alpha, G, want_logits=trace is not None)
         stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         i32 = torch.int32
         cat = lambda k: torch.cat([g[k].to(device=dev, dtype=i32, non_blocking=True).reshape(-1) for g in groups])
@@ -247,7 +255,7 @@ class DecodeEngine(object):
                                     _lib.ptr(t["cross_kv"]), B * S, pw.d, pw.L, stream), "cross_kv")
         _lib.check(lib.itb_init_state(C.byref(cfg), _lib.ptr(t["first"]), _lib.ptr(t["grp_max_len"]), stream), "init_state")
         src_mask = True if has_mask else None
-        key = (pw.uid, B, beam, S, T_max, has_mask, pad, eos, float(alpha), G)
+        key = (pw.uid, B, beam, S, T_max, has_mask, pad, eos, float(alpha), G, trace is not None)
         dec = self._decoder(key, cfg)
         n_steps = max(int(max_len) - 1, 0)
         if trace is None and self.use_graph and n_steps > 0:

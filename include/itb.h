@@ -32,7 +32,9 @@ enum { ITB_GEMM_AUTO = 0, ITB_GEMM_SIMT = 1, ITB_GEMM_TCGEN05 = 2 };
 /* GEMM epilogues */
 enum { ITB_EPI_BIAS_F32 = 0,      /* out f32  = acc + bias                                  */
        ITB_EPI_BIAS_GELU_ACT = 1, /* out act  = gelu_erf(acc + bias)  (HF BertIntermediate) */
-       ITB_EPI_BIAS_ACT = 2 };    /* out act  = acc + bias                                  */
+       ITB_EPI_BIAS_ACT = 2,      /* out act  = acc + bias                                  */
+       /* internal to the fused vocabulary projection (csrc/gemm_tc.cu): per-chunk max / sum-exp / top-K, K = 4, 8, 16 */
+       ITB_EPI_VOCAB_K4 = 3, ITB_EPI_VOCAB_K8 = 4, ITB_EPI_VOCAB_K16 = 5 };
 
 /* Control block living in device memory (see csrc/common.cuh for field meaning). */
 typedef struct { int step, done, steps_run, cur, fin_rows, sent_done, max_len, pad_; } itb_ctl;
@@ -58,7 +60,8 @@ typedef struct {
 typedef struct {
   int dtype, gemm_impl;
   int B, beam, d, H, F, L, V, S, T_max;     /* M = B*beam rows; S = memory length; T_max = max tokens/row */
-  int pad_id, eos_id, n_chunk, reserved0;
+  int pad_id, eos_id, n_chunk, fused_vocab; /* fused_vocab: the tcgen05 vocabulary GEMM emits the per-chunk partials itself
+                                             * (16-bit modes); then n_chunk = itb_vocab_chunks(V) and `logits` may be NULL */
   float len_alpha, ln_eps;                  /* length-penalty exponent (seq_gen.py:43); LayerNorm eps     */
   /* decoder embeddings (f32 tables) -- HF BertEmbeddings */
   const float *emb_word, *emb_pos, *emb_type, *emb_ln_g, *emb_ln_b;
@@ -99,6 +102,7 @@ typedef struct itb_decoder itb_decoder;
 int         itb_abi_version(void);
 const char* itb_last_error(void);
 int         itb_topk_capacity(int beam);
+int         itb_vocab_chunks(int V);      /* n_chunk of the fused vocabulary projection: 2 * ceil(V / 256) */
 int         itb_sizeof_config(void);      /* sizeof(itb_config) / sizeof(itb_layer): binding self-check */
 int         itb_sizeof_layer(void);   /* KT: candidate slots per chunk for this beam width */
 
