@@ -129,40 +129,50 @@ def run_reference(args, rank):
                 ms_per_step=ms)
 
 
-def time_kernel_rooflines(gen, model, peaks):
-    """Times the dominant kernels ALONE with CUDA events on the launching stream (burst peak applies)."""
+def time_kernel_rooflines(gen, model, peaks, rows):
+    """Times the dominant kernel of the step -- the fused vocabulary projection (tcgen05 GEMM whose epilogue emits the
+    softmax / top-k partials) -- ALONE at the super-batch row count, with CUDA events on the launching stream and L2
+    flushed between launches.  At these row counts it is tensor-bound: algorithmic flops = 2 * rows * V * d."""
     import ctypes as C
     from imagetranslate_b200 import _lib
     dev = torch.device("cuda", torch.cuda.current_device())
     pw = gen._weights(model, 1, _lib.BF16, dev)
-    M, d, V = 244, pw.d, pw.V
-    V4 = (V + 3) // 4 * 4
-    x = torch.randn(M, d, device=dev).to(torch.bfloat16)
-    logits = torch.empty(M, V4, device=dev)
-    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     lib = _lib.lib()
+    M, d, V = rows, pw.d, pw.V
+    nc, KT = lib.itb_vocab_chunks(V), lib.itb_topk_capacity(BEAM)
+    x = torch.randn(M, d, device=dev).to(torch.bfloat16)
+    cand_val = torch.empty(M, nc, KT, device=dev)
+    cand_idx = torch.empty(M, nc, KT, dtype=torch.int32, device=dev)
+    cmax, csum = torch.empty(M, nc, device=dev), torch.empty(M, nc, device=dev)
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    res = {}
 
-    def timeit(fn, n=20):
-        for _ in range(3):
-            fn()
-        tot = 0.0
-        for _ in range(n):
-            flush.zero_()                       # L2 flush between timed launches
-            e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
-            e0.record(); fn(); e1.record(); e1.synchronize()
-            tot += e0.elapsed_time(e1)
-        return tot / n
+    def fn():
+        _lib.check(lib.itb_vocab_partials(_lib.BF16, BEAM, _lib.ptr(x), _lib.ptr(pw.w_vocab), _lib.ptr(pw.b_vocab), M, V, d,
+                                          _lib.ptr(cand_val), _lib.ptr(cand_idx), _lib.ptr(cmax), _lib.ptr(csum), None, stream))
 
-    ms = timeit(lambda: _lib.check(lib.itb_linear(_lib.BF16, _lib.GEMM_AUTO, _lib.EPI_BIAS_F32, _lib.ptr(x), _lib.ptr(pw.w_vocab),
-                                                  _lib.ptr(pw.b_vocab), _lib.ptr(logits), M, V, d, V4, stream)))
-    bytes_alg = V * d * 2 + M * d * 2 + M * V * 4
-    hbm = peaks.get("hbm_gbs", 6650.0)
-    res["vocab_gemm"] = dict(bound="hbm", achieved=bytes_alg / ms / 1e6, peak=hbm, unit="GB/s", frac=bytes_alg / ms / 1e6 / hbm,
-                             traffic=None, kernel="gemm_tc_kernel<256,bias_f32> M=244 N=60000 K=768", ms=ms,
-                             tflops=2.0 * M * V * d / ms / 1e9)
-    return res
+    for _ in range(3):
+        fn()
+    tot, n = 0.0, 20
+    for _ in range(n):
+        flush.zero_()                       # L2 flush between timed launches
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record(); fn(); e1.record(); e1.synchronize()
+        tot += e0.elapsed_time(e1)
+    ms = tot / n
+    tf = 2.0 * M * V * d / ms / 1e9
+    peak = peaks.get("bf16_tflops", 1590.0)
+    traffic = None
+    try:        # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at this shape, from the committed ncu capture
+        tj = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))
+        if tj.get("rows") == M and tj.get("V") == V:
+            traffic = tj["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    return dict(bound="tensor", achieved=tf, peak=peak, unit="TFLOP/s", frac=tf / peak, traffic=traffic,
+                kernel="gemm_tc_kernel<256, vocab-partials> rows=%d V=%d K=%d (fused logits + softmax/top-k partials)" % (M, V, d),
+                ms=ms, algorithmic_bytes=V * d * 2 + M * d * 2 + M * nc * (2 + 2 * KT) * 4,
+                hbm_gbs_at_algorithmic_bytes=(V * d * 2 + M * d * 2 + M * nc * (2 + 2 * KT) * 4) / ms / 1e6)
 
 
 def run_b200(args, rank, world, local_rank):
@@ -246,9 +256,8 @@ def run_b200(args, rank, world, local_rank):
         except Exception:
             pass
         if args.dtype != "fp32":
-            rf = time_kernel_rooflines(gen, model, peaks)
-            line["roofline"] = rf["vocab_gemm"]
-            line["roofline"]["peak_source"] = "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650 GB/s"
+            line["roofline"] = time_kernel_rooflines(gen, model, peaks, args.rows)
+            line["roofline"]["peak_source"] = "MEASURED_PEAKS.json bf16_tflops (burst, kernel timed alone)" if peaks else "fallback 1590 TFLOP/s"
         if world == 1 and not args.no_cpu_baseline:
             cb = run_reference(argparse.Namespace(**dict(vars(args), steps=1, warmup=0)), 0)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}

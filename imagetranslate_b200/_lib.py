@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libitb.so")
+LIB_PATH = os.environ.get("ITB_LIB") or os.path.join(_HERE, "libitb.so")      # ITB_LIB: A/B builds of the same ABI
 
 F32, BF16, F16 = 0, 1, 2      # (weights, activations): (f32,f32) / (bf16,bf16) / (fp16,fp16); include/itb.h
 GEMM_AUTO, GEMM_SIMT, GEMM_TCGEN05 = 0, 1, 2
@@ -52,6 +52,7 @@ _SIGS = {
     "itb_sizeof_config": (C.c_int, []),
     "itb_sizeof_layer": (C.c_int, []),
     "itb_linear": (C.c_int, [C.c_int, C.c_int, C.c_int, P, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, P]),
+    "itb_vocab_partials": (C.c_int, [C.c_int, C.c_int, P, P, P, C.c_int, C.c_int, C.c_int, P, P, P, P, P, P]),
     "itb_embed_ln": (C.c_int, [C.c_int, P, P, P, P, P, P, P, P, C.c_float, P, P, C.c_int, C.c_int, C.c_int, C.c_int, P]),
     "itb_add_ln": (C.c_int, [C.c_int, P, P, C.c_int, P, P, C.c_float, P, P, C.c_int, C.c_int, P]),
     "itb_self_attention": (C.c_int, [C.c_int, P, P, P, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, P]),

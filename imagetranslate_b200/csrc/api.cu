@@ -109,6 +109,18 @@ int itb_linear(int dtype, int impl, int epi, const void* A, const void* W, const
     return l.run(dtype, nullptr, (cudaStream_t)stream);
 }
 
+int itb_vocab_partials(int dtype, int beam, const void* x, const void* w_vocab, const float* b_vocab, int rows, int V, int K,
+                       float* cand_val, int* cand_idx, float* chunk_max, float* chunk_sum, float* logits, void* stream) {
+    ITB_REQUIRE(dtype == ITB_BF16 || dtype == ITB_F16, "vocab_partials: the fused vocabulary projection needs 16-bit operands");
+    ITB_REQUIRE(beam >= 1 && beam <= 16 && rows >= 1 && V >= 1, "vocab_partials: bad sizes");
+    CUtensorMap tx, tw;
+    int r = itb_make_tmap_16b(&tx, x, rows, K, 128, dtype == ITB_F16 ? 1 : 0);
+    if (r == 0) r = itb_make_tmap_16b(&tw, w_vocab, V, K, 256, dtype == ITB_F16 ? 1 : 0);
+    if (r != 0) return r;
+    return itb_gemm_tc_vocab(itb_topk_capacity(beam), &tx, &tw, nullptr, b_vocab, rows, V, K, dtype == ITB_F16 ? 1 : 0, cand_val, cand_idx,
+                             chunk_max, chunk_sum, logits, (V + 3) / 4 * 4, itb_vocab_chunks(V), (cudaStream_t)stream);
+}
+
 int itb_cross_kv(int dtype, int impl, const void* memory, const void* w_ckv, const float* b_ckv, void* cross_kv,
                  int rows, int d, int L, void* stream) {
     return itb_linear(dtype, impl, ITB_EPI_BIAS_ACT, memory, w_ckv, b_ckv, cross_kv, rows, L * 2 * d, d, L * 2 * d, stream);

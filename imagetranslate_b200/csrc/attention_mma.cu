@@ -25,8 +25,14 @@
 #define DH 64
 #define AM_WARPS 4
 #define AM_THREADS (AM_WARPS * 32)
+#ifndef AM_STAGE
 #define AM_STAGE 64            // virtual positions staged in shared memory per round trip
+#endif
+#ifndef AM_MINB
+#define AM_MINB 3
+#endif
 #define AM_ROWB 272            // bytes per staged row: K 128 + V 128 + 16 pad
+#define AM_NCH (AM_STAGE / 32)  // 32-position chunks per stage
 #define AM_SMEM (AM_WARPS * AM_STAGE * AM_ROWB)
 
 struct AttnMmaArgs {
@@ -76,7 +82,7 @@ __device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t&
 }
 
 template <typename T, bool SELF>
-__global__ void __launch_bounds__(AM_THREADS, 3) attn_mma_kernel(AttnMmaArgs a) {
+__global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaArgs a) {
     pdl_trigger();
     pdl_wait();
     const int lane = threadIdx.x & 31, nl = lane >> 2, c = lane & 3;       // nl: B-fragment column / C row; c: quad lane
@@ -185,9 +191,9 @@ __global__ void __launch_bounds__(AM_THREADS, 3) attn_mma_kernel(AttnMmaArgs a) 
 
     for (int sb = 0; sb < nv; sb += AM_STAGE) {
         // ---- virtual positions sb + 32*hv + lane: row index and meta = owner mask (bits 0-3) | masked-source (bit 4) ----
-        int rowidx[2], meta[2];
+        int rowidx[AM_NCH], meta[AM_NCH];
 #pragma unroll
-        for (int hv = 0; hv < 2; ++hv) {
+        for (int hv = 0; hv < AM_NCH; ++hv) {
             rowidx[hv] = -1; meta[hv] = 0;
             const int v = sb + 32 * hv + lane;
             if (v < nv) {
@@ -207,7 +213,7 @@ __global__ void __launch_bounds__(AM_THREADS, 3) attn_mma_kernel(AttnMmaArgs a) 
                 }
             }
         }
-        const int nchunk = (nv - sb > 32) ? 2 : 1;                   // 32-position chunks in this stage (warp-uniform)
+        const int nchunk = min(AM_NCH, (nv - sb + 31) >> 5);         // 32-position chunks in this stage (warp-uniform)
 #pragma unroll
         for (int k = 0; k < AM_STAGE / 2; ++k) {
             if (k < 16 * nchunk) {
@@ -223,7 +229,7 @@ __global__ void __launch_bounds__(AM_THREADS, 3) attn_mma_kernel(AttnMmaArgs a) 
         __syncwarp();
 
 #pragma unroll
-        for (int cb = 0; cb < 2; ++cb) {
+        for (int cb = 0; cb < AM_NCH; ++cb) {
             if (cb < nchunk) {
                 const unsigned char* wc = ws + cb * 32 * AM_ROWB;
                 // ---- S = Q.K^T for 4 tiles of 8 positions ----

@@ -115,6 +115,15 @@ int         itb_sizeof_layer(void);   /* KT: candidate slots per chunk for this 
 int itb_linear(int dtype, int impl, int epi, const void* A, const void* W, const float* bias, void* out,
                int M, int N, int K, int ldo, void* stream);
 
+/* Fused vocabulary projection of the 16-bit modes (tcgen05): logits = x[rows][K] . w_vocab[V][K]^T + b_vocab are produced
+ * in TMEM and reduced in the GEMM epilogue to, per (row, chunk c of 128 vocabulary entries; n_chunk = itb_vocab_chunks(V)):
+ *   chunk_max[row][c], chunk_sum[row][c] = sum exp(logit - chunk_max), and the chunk's top-KT (logit, index) pairs
+ *   cand_val / cand_idx [row][c][KT], KT = itb_topk_capacity(beam) -- everything log_softmax + topk need
+ * (reference src/bert_seq2seq.py:6-12 + src/seq_gen.py:194,203) without an (M,V) tensor in HBM.
+ * `logits` ([rows][ceil4(V)] fp32) is optional (parity traces); pass NULL in production. */
+int itb_vocab_partials(int dtype, int beam, const void* x, const void* w_vocab, const float* b_vocab, int rows, int V, int K,
+                       float* cand_val, int* cand_idx, float* chunk_max, float* chunk_sum, float* logits, void* stream);
+
 /* x = LayerNorm(word[tok] + pos[step-1] + type[lang]); HF BertEmbeddings (Appendix A.2), for the ONE
  * new token of each row (reference recomputes the whole prefix: src/seq_gen.py:164-166). */
 int itb_embed_ln(int dtype, const itb_ctl* ctl, const int* tokens, const int* tgt_lang, const float* word,

@@ -57,6 +57,50 @@ def test_linear_fp16(impl, M, N, K):
     assert out2.dtype == torch.float16 and rel_err(out2.float(), torch.nn.functional.gelu(ref)) < 1e-3
 
 
+@pytest.mark.parametrize("dtype", [_lib.BF16, _lib.F16], ids=["bf16", "fp16"])
+@pytest.mark.parametrize("rows,V,beam", [(5, 300, 4), (130, 1000, 3), (244, 60000, 4), (40, 5003, 8), (33, 777, 12), (260, 4096, 1)])
+def test_fused_vocab_projection_partials(dtype, rows, V, beam):
+    """itb_vocab_partials: per-chunk max / sum-exp / top-KT emitted by the GEMM epilogue reproduce log_softmax's
+    log-sum-exp and the row top-k (value desc, index asc) of the full logits; the optional logits output equals the GEMM."""
+    lib, K = _lib.lib(), 768
+    act = ACT[dtype]
+    x, w, b = _rand((rows, K), 31, 1.0, act), _rand((V, K), 32, 0.05, act), _rand((V,), 33)
+    nc, KT, V4 = lib.itb_vocab_chunks(V), lib.itb_topk_capacity(beam), (V + 3) // 4 * 4
+    assert nc == 2 * ((V + 255) // 256)
+    cand_val = torch.full((rows, nc, KT), float("nan"), device=DEV)
+    cand_idx = torch.full((rows, nc, KT), -7, dtype=torch.int32, device=DEV)
+    cmax, csum = torch.full((rows, nc), float("nan"), device=DEV), torch.full((rows, nc), float("nan"), device=DEV)
+    logits = torch.full((rows, V4), float("nan"), device=DEV)
+    for lg in (logits, None):
+        _lib.check(lib.itb_vocab_partials(dtype, beam, _lib.ptr(x), _lib.ptr(w), _lib.ptr(b), rows, V, K, _lib.ptr(cand_val),
+                                          _lib.ptr(cand_idx), _lib.ptr(cmax), _lib.ptr(csum), _lib.ptr(lg), stream()), "vocab_partials")
+        torch.cuda.synchronize()
+    ref = (x.double() @ w.double().t() + b.double())
+    got = logits[:, :V]
+    assert torch.isfinite(got).all() and rel_err(got, ref) < 2e-5
+    # log-sum-exp from the partials (empty chunks carry max = -inf, sum = 0)
+    mm = cmax.max(dim=1, keepdim=True).values
+    lse = mm.squeeze(1).double() + torch.log((csum.double() * torch.exp((cmax - mm).double())).sum(1))
+    assert float((lse - torch.logsumexp(got.double(), 1)).abs().max()) < 2e-5
+    # chunk maxima are the maxima of their 128-entry slices of the kernel's own logits
+    pad = torch.full((rows, nc * 128 - V), float("-inf"), device=DEV)
+    sl = torch.cat([got, pad], 1).view(rows, nc, 128)
+    assert torch.equal(cmax, sl.max(dim=2).values)
+    # per-chunk candidates: sorted top-KT of the slice, lowest index first among equals, -inf / -1 when the slice runs out
+    order = torch.argsort(sl, dim=2, descending=True, stable=True)[:, :, :KT]
+    want_val = torch.gather(sl, 2, order)
+    want_idx = (order + (torch.arange(nc, device=DEV) * 128)[None, :, None]).to(torch.int32)
+    want_idx = torch.where(torch.isinf(want_val), torch.full_like(want_idx, -1), want_idx)
+    assert torch.equal(cand_val, want_val)
+    assert torch.equal(cand_idx, want_idx)
+    # and therefore the row top-k of the candidates is the row top-k of the logits
+    k = min(beam, V)
+    top = torch.topk(got, k, dim=1)
+    flat_v, flat_i = cand_val.view(rows, -1), cand_idx.view(rows, -1)
+    tv, tp = torch.topk(flat_v, k, dim=1)
+    assert torch.equal(tv, top.values)
+
+
 def test_linear_tcgen05_back_to_back_is_deterministic():
     A, W, b = _rand((244, 768), 7, 1.0, torch.bfloat16), _rand((3072, 768), 8, 0.05, torch.bfloat16), _rand((3072,), 9)
     o1 = linear(_lib.BF16, _lib.GEMM_TCGEN05, _lib.EPI_BIAS_F32, A, W, b)

@@ -50,6 +50,14 @@ if "ffn2" in OPS:
     gemm(d, F, _lib.EPI_BIAS_F32)
 if "vocab" in OPS:
     gemm(V, d, _lib.EPI_BIAS_F32)
+if "vocabf" in OPS:      # fused vocabulary projection (logits never leave the SM)
+    W, bias, A = rnd(V, d, dt=ACT, scale=0.02), rnd(V), rnd(M, d, dt=ACT)
+    nc, KT = lib.itb_vocab_chunks(V), lib.itb_topk_capacity(beam)
+    cv, ci = torch.empty(M, nc, KT, device=DEV), torch.empty(M, nc, KT, dtype=torch.int32, device=DEV)
+    cm, cs = torch.empty(M, nc, device=DEV), torch.empty(M, nc, device=DEV)
+    for _ in range(REP):
+        _lib.check(lib.itb_vocab_partials(DT, beam, _lib.ptr(A), _lib.ptr(W), _lib.ptr(bias), M, V, d, _lib.ptr(cv), _lib.ptr(ci),
+                                          _lib.ptr(cm), _lib.ptr(cs), None, st()))
 if "addln" in OPS:
     y, xf, xa, g_, b_ = rnd(M, d), rnd(M, d), rnd(M, d, dt=ACT), rnd(d), rnd(d)
     for _ in range(REP):
