@@ -38,7 +38,7 @@ def parse():
     ap.add_argument("--rows", type=int, default=4096, help="beam rows per super-batch (consecutive reference batches decoded in lockstep)")
     ap.add_argument("--lanes", type=int, default=2, help="batches in flight per GPU (separate streams; results do not depend on it)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-sentences", type=int, default=6)
+    ap.add_argument("--cpu-sentences", type=int, default=4)
     return ap.parse_args()
 
 
@@ -111,10 +111,11 @@ def run_reference(args, rank):
     tp = R.FakeTextProcessor(VOCAB)
     torch.manual_seed(0)
     model = R.Seq2SeqModel(tp, lang_dec=False, tie_embed=False, enc_layer=ENC, dec_layer=DEC).eval()
-    b = build_batches(args.sentences, 1234, args.batch, args.capacity)[0]
+    bs = build_batches(args.sentences, 1234, args.batch, args.capacity)
+    b = bs[len(bs) // 2]                 # the median-length batch of the workload (the first one holds the shortest sentences)
     n = args.cpu_sentences
     kw = batch_kwargs({k: (v[:n] if v.dim() > 0 and v.size(0) >= n else v) for k, v in b.items()})
-    sample = "first %d sentences of the first batch (src len %d, full max_len), fp32, %d threads" % (
+    sample = "first %d sentences of the median-length batch (src len %d, full max_len), fp32, %d threads" % (
         n, b["src_texts"].size(1), torch.get_num_threads())
     times, toks = [], 0
     for it in range(args.warmup + args.steps):

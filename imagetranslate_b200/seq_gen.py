@@ -7,6 +7,7 @@ The search itself (decoder step, vocabulary projection, log-softmax, scoring, to
 termination) runs in CUDA kernels -- see include/itb.h.  The encoder memory still comes from the
 model's own `encode` (:96,99,106), exactly as in the reference.
 """
+import os
 import threading
 from concurrent.futures import ThreadPoolExecutor
 
@@ -50,6 +51,9 @@ class BeamDecoder(nn.Module):
         self._lane = threading.local()      # forward_many: which engine (workspace + stream) this thread drives
         self._lock = threading.Lock()
         self.kernel_launches = 0            # kernels enqueued by this decoder so far (bench.py's gpu_launches)
+        # forward_many packs consecutive batches into one super-batch while their memory lengths stay within this ratio
+        # (rows of the shorter batches idle once their own search has ended)
+        self.pack_ratio = float(os.environ.get("ITB_PACK_RATIO", "1.5"))
 
     def len_penalty(self, lengths: torch.Tensor):
         """reference src/seq_gen.py:37-44 (kept for callers; the kernels compute it on device)."""
@@ -193,7 +197,7 @@ class BeamDecoder(nn.Module):
             S = int(src.size(1)) if src is not None else 49
             key = (int(tl[0]), beam, kw.get("pad_idx"), src is None, kw.get("max_len"))
             n = int(first.numel()) * beam
-            ok = cur and key == cur_key and cur_rows + n <= rows and max(s_hi, S) <= 1.5 * min(s_lo, S)
+            ok = cur and key == cur_key and cur_rows + n <= rows and max(s_hi, S) <= self.pack_ratio * min(s_lo, S)
             if not ok:
                 if cur:
                     packs.append(cur)
