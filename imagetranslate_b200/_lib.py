@@ -54,6 +54,7 @@ _SIGS = {
     "itb_linear": (C.c_int, [C.c_int, C.c_int, C.c_int, P, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, P]),
     "itb_vocab_partials": (C.c_int, [C.c_int, C.c_int, P, P, P, C.c_int, C.c_int, C.c_int, P, P, P, P, P, P]),
     "itb_embed_ln": (C.c_int, [C.c_int, P, P, P, P, P, P, P, P, C.c_float, P, P, C.c_int, C.c_int, C.c_int, C.c_int, P]),
+    "itb_embed_seq_ln": (C.c_int, [C.c_int, P, P, P, P, P, P, P, C.c_float, P, P, C.c_int, C.c_int, C.c_int, P]),
     "itb_add_ln": (C.c_int, [C.c_int, P, P, C.c_int, P, P, C.c_float, P, P, C.c_int, C.c_int, P]),
     "itb_self_attention": (C.c_int, [C.c_int, P, P, P, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, P]),
     "itb_cross_attention": (C.c_int, [C.c_int, P, P, P, P, C.c_int, P, C.c_int, P, P, C.c_int, C.c_int, C.c_int, C.c_int,

@@ -89,6 +89,33 @@ __global__ void __launch_bounds__(32 * LN_ROWS, 4) embed_ln_kernel(const ItbCtl*
     ln_row_write<TA>(v, nv, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, lane);
 }
 
+// Encoder embeddings: every position of the padded source batch at once.  x[b*S + p] = LN(word[tok] + pos[p] + type[lang[b]])
+// (HF BertEmbeddings with position_ids = arange(S); reference src/bert_seq2seq.py:103-129, token types = source language).
+template <typename TA>
+__global__ void __launch_bounds__(32 * LN_ROWS, 4) embed_seq_ln_kernel(const int* __restrict__ tokens, const int* __restrict__ lang,
+                                                               const float* __restrict__ word, const float* __restrict__ pos,
+                                                               const float* __restrict__ type, const float* __restrict__ g,
+                                                               const float* __restrict__ b, float eps, float* __restrict__ x_f32,
+                                                               TA* __restrict__ x_act, int rows, int S, int d) {
+    const int lane = threadIdx.x & 31, r = blockIdx.x * LN_ROWS + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int tok = tokens[r], p = r % S, lg = lang[r / S];
+    const int nv = (d + 127) / 128;
+    float4 v[LN_MAXV];
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i) {
+        const int c = (i * 32 + lane) * 4;
+        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < nv && c < d) {
+            const float4 a = *reinterpret_cast<const float4*>(word + (size_t)tok * d + c);
+            const float4 e = *reinterpret_cast<const float4*>(pos + (size_t)p * d + c);
+            const float4 t = *reinterpret_cast<const float4*>(type + (size_t)lg * d + c);
+            v[i] = make_float4(a.x + e.x + t.x, a.y + e.y + t.y, a.z + e.z + t.z, a.w + e.w + t.w);
+        }
+    }
+    ln_row_write<TA>(v, nv, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, lane);
+}
+
 template <typename TA>
 __global__ void __launch_bounds__(32 * LN_ROWS, 4) add_ln_kernel(const ItbCtl* __restrict__ ctl, const float* __restrict__ y,
                                                      int n_partial, const float* __restrict__ g,
@@ -220,6 +247,21 @@ int itb_embed_ln(int dtype, const itb_ctl* ctl, const int* tokens, const int* tg
                        x_f32, (float*)x_act, M, beam, d, T_max);
     if (e != cudaSuccess) { itb_set_error("embed_ln: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("embed_ln");
+}
+
+int itb_embed_seq_ln(int dtype, const int* tokens, const int* lang, const float* word, const float* pos, const float* type,
+                     const float* g, const float* b, float eps, float* x_f32, void* x_act, int B, int S, int d, void* stream) {
+    ITB_REQUIRE(d % 128 == 0 && d <= 1024 && B > 0 && S > 0, "embed_seq_ln: d must be a multiple of 128, at most 1024");
+    const int rows = B * S;
+    const dim3 lgrid((rows + LN_ROWS - 1) / LN_ROWS), lblock(32 * LN_ROWS);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == ITB_BF16)
+        embed_seq_ln_kernel<__nv_bfloat16><<<lgrid, lblock, 0, s>>>(tokens, lang, word, pos, type, g, b, eps, x_f32, (__nv_bfloat16*)x_act, rows, S, d);
+    else if (dtype == ITB_F16)
+        embed_seq_ln_kernel<__half><<<lgrid, lblock, 0, s>>>(tokens, lang, word, pos, type, g, b, eps, x_f32, (__half*)x_act, rows, S, d);
+    else
+        embed_seq_ln_kernel<float><<<lgrid, lblock, 0, s>>>(tokens, lang, word, pos, type, g, b, eps, x_f32, (float*)x_act, rows, S, d);
+    return itb_check_launch("embed_seq_ln");
 }
 
 int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, int n_partial, const float* g, const float* b, float eps,

@@ -94,6 +94,54 @@ class PackedDecoder(object):
         return tuple(t._version for t in self._src) != self.versions
 
 
+class PackedEncoder(object):
+    """Device-resident weights of the bidirectional text encoder in kernel layout (reference src/bert_seq2seq.py:94-144;
+    state-dict names encoder.embeddings.*, encoder.encoder.layer.N.attention.{self.{query,key,value},output.dense,
+    output.LayerNorm}, .intermediate.dense, .output.{dense,LayerNorm}).  key|value are stacked into one [2d][d] matrix so
+    that their GEMM writes the [position][K|V] rows the attention kernels read."""
+
+    def __init__(self, encoder, dtype_code, device):
+        act = _WT[dtype_code]
+        self.dtype_code = dtype_code
+        self._src = []
+
+        def f32(t):
+            self._src.append(t)
+            return t.detach().to(device=device, dtype=torch.float32).contiguous()
+
+        def mat(t):
+            self._src.append(t)
+            return t.detach().to(device=device, dtype=act).contiguous()
+
+        emb = encoder.embeddings
+        self.emb_word, self.emb_pos, self.emb_type = (f32(emb.word_embeddings.weight), f32(emb.position_embeddings.weight),
+                                                      f32(emb.token_type_embeddings.weight))
+        self.emb_ln_g, self.emb_ln_b = f32(emb.LayerNorm.weight), f32(emb.LayerNorm.bias)
+        self.ln_eps = float(emb.LayerNorm.eps)
+        self.d = emb.word_embeddings.weight.shape[1]
+        layers = encoder.encoder.layer
+        self.H = layers[0].attention.self.num_attention_heads
+        self.F = layers[0].intermediate.dense.weight.shape[0]
+        self.layers = []
+        for ly in layers:
+            sa = ly.attention
+            for m in (sa.self.key, sa.self.value):
+                self._src.extend([m.weight, m.bias])
+            self.layers.append(dict(
+                w_q=mat(sa.self.query.weight), b_q=f32(sa.self.query.bias),
+                w_kv=torch.cat([sa.self.key.weight, sa.self.value.weight], 0).detach().to(device, act).contiguous(),
+                b_kv=torch.cat([sa.self.key.bias, sa.self.value.bias], 0).detach().to(device, torch.float32).contiguous(),
+                w_o=mat(sa.output.dense.weight), b_o=f32(sa.output.dense.bias),
+                ln1_g=f32(sa.output.LayerNorm.weight), ln1_b=f32(sa.output.LayerNorm.bias),
+                w_1=mat(ly.intermediate.dense.weight), b_1=f32(ly.intermediate.dense.bias),
+                w_2=mat(ly.output.dense.weight), b_2=f32(ly.output.dense.bias),
+                ln2_g=f32(ly.output.LayerNorm.weight), ln2_b=f32(ly.output.LayerNorm.bias)))
+        self.versions = tuple(t._version for t in self._src)
+
+    def stale(self):
+        return tuple(t._version for t in self._src) != self.versions
+
+
 class Workspace(object):
     """Flat device buffers that only ever grow; indexing always uses the CURRENT batch shape."""
 
@@ -199,6 +247,42 @@ class DecodeEngine(object):
         t["first"], t["grp_max_len"] = ws.get("first", B, i32), ws.get("grp_max_len", G, i32)
         t["memory"] = ws.get("memory", B * S * pw.d, act)
         return c, t
+
+    @torch.no_grad()
+    def encode(self, pe, src_inputs, src_mask, src_langs):
+        """Encoder forward of one padded source batch on the C-ABI kernels (replaces reference src/seq2seq.py:101-108 ->
+        src/bert_seq2seq.py:103-144, HF BertLayer without cross-attention: Appendix A.3-A.6): embeddings+LN, then per layer
+        Q / K|V projections, bidirectional attention with the additive -10000 padding mask (every position of a sentence is
+        a query over the sentence's K,V rows: the single-query kernels with beam := S), output projection + residual + LN,
+        FFN1 + erf-GELU, FFN2 + residual + LN.  src_inputs (B,S) ints, src_mask (B,S) bool, src_langs (B,) ints.
+        Returns the memory (B,S,d) in the activation dtype (a fresh tensor)."""
+        lib, dev, ws, code = self.lib, self.device, self.ws, self.dtype_code
+        act, f32, i32 = _ACT[code], torch.float32, torch.int32
+        B, S = int(src_inputs.shape[0]), int(src_inputs.shape[1])
+        d, H, F, rows = pe.d, pe.H, pe.F, B * S
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        tok = src_inputs.to(device=dev, dtype=i32, non_blocking=True).contiguous()
+        lang = src_langs.to(device=dev, dtype=i32, non_blocking=True).contiguous()
+        mask = src_mask.to(device=dev, non_blocking=True).to(torch.uint8).contiguous()
+        x_f32, x_act = ws.get("enc_x_f32", rows * d, f32), ws.get("enc_x_act", rows * d, act)
+        q, kv = ws.get("enc_q", rows * d, f32), ws.get("enc_kv", rows * 2 * d, act)
+        ctx, y, h = ws.get("enc_ctx", rows * d, act), ws.get("enc_y", rows * d, f32), ws.get("enc_h", rows * F, act)
+        P, impl = _lib.ptr, self.gemm_impl
+        _lib.check(lib.itb_embed_seq_ln(code, P(tok), P(lang), P(pe.emb_word), P(pe.emb_pos), P(pe.emb_type), P(pe.emb_ln_g),
+                                        P(pe.emb_ln_b), pe.ln_eps, P(x_f32), P(x_act), B, S, d, stream), "embed_seq_ln")
+        for w in pe.layers:
+            _lib.check(lib.itb_linear(code, impl, _lib.EPI_BIAS_F32, P(x_act), P(w["w_q"]), P(w["b_q"]), P(q), rows, d, d, d, stream), "enc q")
+            _lib.check(lib.itb_linear(code, impl, _lib.EPI_BIAS_ACT, P(x_act), P(w["w_kv"]), P(w["b_kv"]), P(kv), rows, 2 * d, d, 2 * d,
+                                      stream), "enc kv")
+            _lib.check(lib.itb_cross_attention(code, None, None, None, P(q), d, P(kv), 0, P(mask), P(ctx), rows, S, d, H, S, 1, stream),
+                       "enc attention")
+            _lib.check(lib.itb_linear(code, impl, _lib.EPI_BIAS_F32, P(ctx), P(w["w_o"]), P(w["b_o"]), P(y), rows, d, d, d, stream), "enc o")
+            _lib.check(lib.itb_add_ln(code, None, P(y), 1, P(w["ln1_g"]), P(w["ln1_b"]), pe.ln_eps, P(x_f32), P(x_act), rows, d, stream), "enc ln1")
+            _lib.check(lib.itb_linear(code, impl, _lib.EPI_BIAS_GELU_ACT, P(x_act), P(w["w_1"]), P(w["b_1"]), P(h), rows, F, d, F, stream), "enc ffn1")
+            _lib.check(lib.itb_linear(code, impl, _lib.EPI_BIAS_F32, P(h), P(w["w_2"]), P(w["b_2"]), P(y), rows, d, F, d, stream), "enc ffn2")
+            _lib.check(lib.itb_add_ln(code, None, P(y), 1, P(w["ln2_g"]), P(w["ln2_b"]), pe.ln_eps, P(x_f32), P(x_act), rows, d, stream), "enc ln2")
+        self.enc_launches = 1 + 8 * len(pe.layers)
+        return x_act[:rows * d].view(B, S, d).clone()
 
     @torch.no_grad()
     def decode(self, pw, memory, src_mask, first_tokens, tgt_type_ids, max_lens, max_len, beam, pad, eos, alpha, trace=None):

@@ -15,7 +15,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from .engine import DecodeEngine, PackedDecoder
+from .engine import DecodeEngine, PackedDecoder, PackedEncoder
 
 
 def get_outputs_until_eos(eos, outputs, size_limit=None, remove_first_token: bool = False):
@@ -54,6 +54,8 @@ class BeamDecoder(nn.Module):
         # forward_many packs consecutive batches into one super-batch while their memory lengths stay within this ratio
         # (rows of the shorter batches idle once their own search has ended)
         self.pack_ratio = float(os.environ.get("ITB_PACK_RATIO", "1.5"))
+        # text memory: run the encoder on this library's kernels (False / ITB_TORCH_ENCODER=1: call model.encode instead)
+        self.cuda_encoder = os.environ.get("ITB_TORCH_ENCODER", "0") != "1"
 
     def len_penalty(self, lengths: torch.Tensor):
         """reference src/seq_gen.py:37-44 (kept for callers; the kernels compute it on device)."""
@@ -86,6 +88,22 @@ class BeamDecoder(nn.Module):
             pw = PackedDecoder(decoder, out_layer, code, device)
             self._packed[key] = pw
         return pw
+
+    def _enc_weights(self, model, code, device):
+        key = ("enc", code, str(device))
+        with self._lock:
+            pe = self._packed.get(key)
+        if pe is None or pe.stale():
+            pe = PackedEncoder(model.encoder, code, device)
+            self._packed[key] = pe
+        return pe
+
+    @staticmethod
+    def _is_bert_text_encoder(model):
+        enc = getattr(model, "encoder", None)
+        return (enc is not None and hasattr(enc, "embeddings") and hasattr(getattr(enc, "encoder", None), "layer")
+                and all(hasattr(ly, "attention") and hasattr(ly, "intermediate") and not hasattr(ly, "crossattention")
+                        for ly in enc.encoder.layer))
 
     def refresh_weights(self):
         """Drop packed weights (call after loading a new checkpoint into the wrapped model)."""
@@ -125,8 +143,16 @@ class BeamDecoder(nn.Module):
         with torch.no_grad():
             if src_inputs is not None:                            # :94-96
                 src_mask = src_mask.to(device)
-                langs2d = src_langs.unsqueeze(-1).expand(-1, src_inputs.size(-1))
-                memory = model.encode(src_inputs, src_mask, langs2d)[0]
+                code0 = self._dtype_code(wemb)
+                if self.cuda_encoder and self._is_bert_text_encoder(model):
+                    # :96 Seq2Seq.encode -> BertEncoderModel.forward on this library's kernels (engine.encode)
+                    eng = self._engine(device, code0)
+                    memory = eng.encode(self._enc_weights(model, code0, device), src_inputs, src_mask, src_langs)
+                    with self._lock:
+                        self.kernel_launches += eng.enc_launches
+                else:
+                    langs2d = src_langs.unsqueeze(-1).expand(-1, src_inputs.size(-1))
+                    memory = model.encode(src_inputs, src_mask, langs2d)[0]
                 mem_mask = src_mask
             else:
                 if image_embed is None:                           # :97-99

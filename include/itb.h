@@ -130,6 +130,13 @@ int itb_embed_ln(int dtype, const itb_ctl* ctl, const int* tokens, const int* tg
                  const float* pos, const float* type, const float* g, const float* b, float eps, float* x_f32,
                  void* x_act, int M, int beam, int d, int T_max, void* stream);
 
+/* Encoder embeddings for the whole padded source batch: x[b*S+p] = LayerNorm(word[tokens[b][p]] + pos[p] + type[lang[b]]).
+ * HF BertEmbeddings as called by the reference encoder (src/bert_seq2seq.py:103-129; token types = source language,
+ * src/seq_gen.py:94-96).  The rest of the encoder layer stack runs on itb_linear / itb_cross_attention (queries = the S
+ * positions of a sentence, beam := S, L := 1, layer := 0 over a [B][S][1][2][d] K,V buffer) / itb_add_ln. */
+int itb_embed_seq_ln(int dtype, const int* tokens, const int* lang, const float* word, const float* pos, const float* type,
+                     const float* g, const float* b, float eps, float* x_f32, void* x_act, int B, int S, int d, void* stream);
+
 /* x = LayerNorm(sum_{s<n_partial} y[s] + x) in place on x_f32, and act copy.  HF BertSelfOutput / BertOutput
  * (A.4, A.6).  y is [n_partial][M][d]: the split-K partial outputs of the producing GEMM, summed in a fixed order. */
 int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, int n_partial, const float* g, const float* b, float eps,

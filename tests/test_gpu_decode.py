@@ -191,3 +191,40 @@ def test_forward_many_superbatches_and_lanes_equal_sequential(dtype, eos_bias):
         for i in (1, 4):
             want = R.beam_search(cpu, beam_width=4, **cases.GEN, **batches[i])
             assert [o.tolist() for o in seq[i]] == [w.tolist() for w in want]
+
+
+@pytest.mark.parametrize("dtype,tol", [("fp32", 3e-5), ("bf16", 6e-2), ("fp16", 8e-3)])
+@pytest.mark.parametrize("B,S,layers", [(5, 14, 2), (3, 37, 1), (16, 64, 3)])
+def test_encoder_on_cabi_kernels_matches_reference_encoder(dtype, tol, B, S, layers):
+    """engine.encode (embeddings+LN, Q / K|V GEMMs, bidirectional attention with the -10000 padding mask, O GEMM + LN,
+    FFN + LN on the C-ABI kernels) against the reference encoder (oracle restatement of src/bert_seq2seq.py:103-144,
+    fp32 CPU) on a ragged padded batch; compared on the non-padded positions."""
+    tp = R.FakeTextProcessor(1500)
+    torch.manual_seed(60 + layers)
+    model = R.Seq2SeqModel(tp, lang_dec=False, tie_embed=False, enc_layer=layers, dec_layer=1).eval()
+    src, mask, _ = cases.make_text_batch(B, S, 1500, 77 + B)
+    langs = torch.arange(B) % 2
+    with torch.no_grad():
+        want = model.encode(src, mask, langs.unsqueeze(-1).expand(-1, S))[0]
+    m2 = model.to(DEV)
+    bd = BeamDecoder(m2, beam_width=4, dtype=dtype, **cases.GEN)
+    code = bd._dtype_code(m2.encoder.embeddings.word_embeddings.weight)
+    eng = bd._engine(torch.device(DEV), code)
+    got = eng.encode(bd._enc_weights(m2, code, torch.device(DEV)), src, mask, langs)
+    torch.cuda.synchronize()
+    assert got.shape == want.shape and torch.isfinite(got).all()
+    err = (got.float().cpu() - want)[mask].abs().max().item()
+    assert err < tol, err
+    model.cpu()
+
+
+def test_torch_encoder_switch_gives_the_same_hypotheses():
+    """cuda_encoder=False routes the memory through model.encode (PyTorch); fp32 hypotheses are the same either way."""
+    model, kw = _fresh_case(29, 3001, 6, 12, 4, 2)
+    model = model.to(DEV)
+    a, bd = _decode(model, kw, "fp32")
+    bd.cuda_encoder = False
+    kw2 = dict(kw); kw2.pop("beam_width")
+    with torch.no_grad():
+        b = bd(**kw2)
+    assert [x.tolist() for x in a] == [x.tolist() for x in b]
