@@ -101,7 +101,8 @@ template <int MT> struct TcCfg {
     static constexpr int kBudget = (MT <= 64 ? 100 : 200) * 1024;
     static constexpr int kStagesRaw = kBudget / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
-    static constexpr int kTmemCols = (2 * MT) < 32 ? 32 : (2 * MT);            // power of two for MT in {32,64,128,256}
+    // two accumulator buffers of MT columns, rounded up to the power of two tcgen05.alloc wants (MT = 192 -> 512)
+    static constexpr int kTmemCols = (2 * MT) <= 32 ? 32 : (2 * MT) <= 64 ? 64 : (2 * MT) <= 128 ? 128 : (2 * MT) <= 256 ? 256 : 512;
     static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 };
 
@@ -463,7 +464,9 @@ void itb_tc_plan(int M, int N, int K, int max_split, int* mt_out, int* split_out
     const int n_tiles = (N + TC_BN - 1) / TC_BN, KB = K / TC_BK;
     long best_cost = -1;
     *mt_out = 32; *split_out = 1;
-    for (int mt = 32; mt <= 256; mt *= 2) {
+    static const int kTileRows[] = {32, 64, 128, 192, 256};                    // 192: 22 row tiles x 6 = 132 CTAs for N = 768 at M = 4096
+    for (int ti = 0; ti < 5; ++ti) {
+        const int mt = kTileRows[ti];
         for (int sp = 1; sp <= max_split; ++sp) {
             if (KB % sp != 0) continue;
             const long tiles = (long)n_tiles * ((M + mt - 1) / mt) * sp;
@@ -514,6 +517,7 @@ int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const v
         case 32: return launch_tc_epi<32>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, nsplit, s);
         case 64: return launch_tc_epi<64>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, nsplit, s);
         case 128: return launch_tc_epi<128>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, nsplit, s);
+        case 192: return launch_tc_epi<192>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, nsplit, s);
         case 256: return launch_tc_epi<256>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, nsplit, s);
         default: itb_set_error("linear(tcgen05): unsupported tile height %d", mt); return -2;
     }

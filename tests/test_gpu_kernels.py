@@ -31,7 +31,8 @@ def test_linear_f32_cuda_cores(M, N, K, epi):
 
 @pytest.mark.parametrize("impl", [_lib.GEMM_SIMT, _lib.GEMM_TCGEN05], ids=["simt", "tcgen05"])
 @pytest.mark.parametrize("M,N,K", [(7, 256, 64), (32, 768, 768), (60, 2304, 768), (100, 768, 3072), (244, 3072, 768),
-                                   (300, 1000, 768), (940, 768, 768), (244, 60000, 768), (16, 9216, 768)])
+                                   (300, 1000, 768), (940, 768, 768), (244, 60000, 768), (16, 9216, 768),
+                                   (4096, 768, 768), (4000, 768, 3072), (2048, 3072, 768)])
 def test_linear_bf16(impl, M, N, K):
     A, W, b = _rand((M, K), 4, 1.0, torch.bfloat16), _rand((N, K), 5, 0.05, torch.bfloat16), _rand((N,), 6)
     ref = A.double() @ W.double().t() + b.double()
