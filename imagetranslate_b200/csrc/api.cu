@@ -14,9 +14,9 @@ int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const v
                 int M, int N, int K, int ldo, int act_f16, int mt, int nsplit, cudaStream_t s);
 int itb_make_tmap_16b(CUtensorMap* map, const void* base, int rows, int K, int box_rows, int is_f16);
 void itb_tc_plan(int M, int N, int K, int max_split, int* mt_out, int* split_out);
-int itb_gemm_tc_vocab(int kt, const CUtensorMap* tmX, const CUtensorMap* tmWv, const void* ctl, const float* bias, int rows, int V,
-                      int K, int act_f16, float* cand_val, int* cand_idx, float* chunk_max, float* chunk_sum, float* logits,
-                      int ldl, int n_chunk, cudaStream_t s);
+int itb_gemm_tc_vocab(int kt, const CUtensorMap* tmX, const CUtensorMap* tmWv, const CUtensorMap* tmWv128, const void* ctl,
+                      const float* bias, int rows, int V, int K, int act_f16, float* cand_val, int* cand_idx, float* chunk_max,
+                      float* chunk_sum, float* logits, int ldl, int n_chunk, cudaStream_t s);
 
 static thread_local char g_err[512] = "";
 
@@ -85,11 +85,17 @@ struct itb_decoder {
     std::vector<Linear> qkv, o, cq, co, f1, f2;
     Linear vocab;
     bool vocab_fused = false;            // 16-bit modes: vocabulary GEMM with the softmax / top-k partials in its epilogue
-    CUtensorMap tm_vx, tm_vw;            // fused launch: activations [M][d] box 128, vocabulary weights [V][d] box 256
+    CUtensorMap tm_vx, tm_vw, tm_vw2;            // fused launch: activations [M][d] box 128, vocabulary weights [V][d] box 256
     cudaGraphExec_t exec = nullptr;      // `graph_steps` search steps captured once, replayed for the whole batch
     int graph_steps = 0;
     cudaStream_t cap_stream = nullptr;
 };
+
+__global__ void stream_fence_kernel() {}
+
+int itb_cross_attention_impl(int dtype, const itb_ctl* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
+                             const void* cross_kv, int layer, const unsigned char* src_mask, void* ctx, int M, int beam, int d,
+                             int H, int S, int L, int early_kv, void* stream);
 
 extern "C" {
 
@@ -113,17 +119,23 @@ int itb_vocab_partials(int dtype, int beam, const void* x, const void* w_vocab, 
                        float* cand_val, int* cand_idx, float* chunk_max, float* chunk_sum, float* logits, void* stream) {
     ITB_REQUIRE(dtype == ITB_BF16 || dtype == ITB_F16, "vocab_partials: the fused vocabulary projection needs 16-bit operands");
     ITB_REQUIRE(beam >= 1 && beam <= 16 && rows >= 1 && V >= 1, "vocab_partials: bad sizes");
-    CUtensorMap tx, tw;
+    CUtensorMap tx, tw, tw2;
     int r = itb_make_tmap_16b(&tx, x, rows, K, 128, dtype == ITB_F16 ? 1 : 0);
     if (r == 0) r = itb_make_tmap_16b(&tw, w_vocab, V, K, 256, dtype == ITB_F16 ? 1 : 0);
+    if (r == 0) r = itb_make_tmap_16b(&tw2, w_vocab, V, K, 128, dtype == ITB_F16 ? 1 : 0);
     if (r != 0) return r;
-    return itb_gemm_tc_vocab(itb_topk_capacity(beam), &tx, &tw, nullptr, b_vocab, rows, V, K, dtype == ITB_F16 ? 1 : 0, cand_val, cand_idx,
+    return itb_gemm_tc_vocab(itb_topk_capacity(beam), &tx, &tw, &tw2, nullptr, b_vocab, rows, V, K, dtype == ITB_F16 ? 1 : 0, cand_val, cand_idx,
                              chunk_max, chunk_sum, logits, (V + 3) / 4 * 4, itb_vocab_chunks(V), (cudaStream_t)stream);
 }
 
 int itb_cross_kv(int dtype, int impl, const void* memory, const void* w_ckv, const float* b_ckv, void* cross_kv,
                  int rows, int d, int L, void* stream) {
-    return itb_linear(dtype, impl, ITB_EPI_BIAS_ACT, memory, w_ckv, b_ckv, cross_kv, rows, L * 2 * d, d, L * 2 * d, stream);
+    int r = itb_linear(dtype, impl, ITB_EPI_BIAS_ACT, memory, w_ckv, b_ckv, cross_kv, rows, L * 2 * d, d, L * 2 * d, stream);
+    if (r != 0) return r;
+    // A plain (non-programmatic) launch: everything after it in the stream starts only once cross_kv is complete, which
+    // is what lets the decoder's cross-attention fetch K,V ahead of its programmatic-dependency wait.
+    stream_fence_kernel<<<1, 32, 0, (cudaStream_t)stream>>>();
+    return itb_check_launch("cross_kv fence");
 }
 
 int itb_decoder_create(const itb_config* c, itb_decoder** out) {
@@ -159,6 +171,7 @@ int itb_decoder_create(const itb_config* c, itb_decoder** out) {
             d->vocab_fused = true;
             r = itb_make_tmap_16b(&d->tm_vx, c->x_act, M, D, 128, c->dtype == ITB_F16 ? 1 : 0);
             if (r == 0) r = itb_make_tmap_16b(&d->tm_vw, c->w_vocab, c->V, D, 256, c->dtype == ITB_F16 ? 1 : 0);
+            if (r == 0) r = itb_make_tmap_16b(&d->tm_vw2, c->w_vocab, c->V, D, 128, c->dtype == ITB_F16 ? 1 : 0);
         }
     } else if (r == 0 && c->logits == nullptr) {
         itb_set_error("decoder_create: logits buffer missing");
@@ -199,8 +212,8 @@ int itb_decoder_step(itb_decoder* dec, void* stream) {
         ITB_TRY(dec->o[l].run(c.dtype, c.ctl, s));
         ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->o[l].nsplit, w.ln1_g, w.ln1_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
         ITB_TRY(dec->cq[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(itb_cross_attention(c.dtype, c.ctl, c.sent_done, c.mem_len, c.qkv, 3 * D, c.cross_kv, l, c.src_mask, c.ctx, M, c.beam, D, c.H,
-                                    c.S, c.L, stream));
+        ITB_TRY(itb_cross_attention_impl(c.dtype, c.ctl, c.sent_done, c.mem_len, c.qkv, 3 * D, c.cross_kv, l, c.src_mask, c.ctx, M, c.beam, D,
+                                         c.H, c.S, c.L, 1, stream));
         ITB_TRY(dec->co[l].run(c.dtype, c.ctl, s));
         ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->co[l].nsplit, w.ln2_g, w.ln2_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
         ITB_TRY(dec->f1[l].run(c.dtype, c.ctl, s));
@@ -208,7 +221,7 @@ int itb_decoder_step(itb_decoder* dec, void* stream) {
         ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->f2[l].nsplit, w.ln3_g, w.ln3_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
     }
     if (dec->vocab_fused)
-        ITB_TRY(itb_gemm_tc_vocab(itb_topk_capacity(c.beam), &dec->tm_vx, &dec->tm_vw, c.ctl, c.b_vocab, M, c.V, D, c.dtype == ITB_F16 ? 1 : 0,
+        ITB_TRY(itb_gemm_tc_vocab(itb_topk_capacity(c.beam), &dec->tm_vx, &dec->tm_vw, &dec->tm_vw2, c.ctl, c.b_vocab, M, c.V, D, c.dtype == ITB_F16 ? 1 : 0,
                                   c.cand_val, c.cand_idx, c.chunk_max, c.chunk_sum, c.logits, (c.V + 3) / 4 * 4, c.n_chunk, s));
     else
         ITB_TRY(dec->vocab.run(c.dtype, c.ctl, s));

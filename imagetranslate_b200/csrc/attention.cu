@@ -378,7 +378,7 @@ static int launch_cross(const AttnArgs& a, int H, cudaStream_t s) {
 
 int itb_attn_mma(int dtype, bool self, const void* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
                  void* kv, const unsigned char* anc, const unsigned char* mask, void* ctx, int M, int beam, int d, int T_max,
-                 int S, int L, int layer, cudaStream_t s);
+                 int S, int L, int layer, int early_kv, cudaStream_t s);
 
 // 16-bit modes run the tensor-core kernel (attention_mma.cu); fp32 (parity mode) and ITB_ATTN=simt run the CUDA-core one.
 static bool use_mma(int dtype) {
@@ -390,6 +390,10 @@ static bool use_mma(int dtype) {
     return v != 0 && dtype != ITB_F32;
 }
 
+int itb_cross_attention_impl(int dtype, const itb_ctl* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
+                             const void* cross_kv, int layer, const unsigned char* src_mask, void* ctx, int M, int beam, int d,
+                             int H, int S, int L, int early_kv, void* stream);
+
 extern "C" {
 
 int itb_self_attention(int dtype, const itb_ctl* ctl, const int* sent_done, const float* qkv, void* kv_layer,
@@ -398,7 +402,7 @@ int itb_self_attention(int dtype, const itb_ctl* ctl, const int* sent_done, cons
     ITB_REQUIRE(T_max <= 2048, "self_attention: T_max too large for the shared-memory score buffer");
     ITB_REQUIRE(M % beam == 0, "self_attention: M must be a multiple of the beam width");
     if (use_mma(dtype))
-        return itb_attn_mma(dtype, true, ctl, sent_done, nullptr, qkv, 3 * d, kv_layer, anc, nullptr, ctx, M, beam, d, T_max, 0, 0, 0,
+        return itb_attn_mma(dtype, true, ctl, sent_done, nullptr, qkv, 3 * d, kv_layer, anc, nullptr, ctx, M, beam, d, T_max, 0, 0, 0, 0,
                             (cudaStream_t)stream);
     AttnArgs a = {};
     a.ctl = reinterpret_cast<const ItbCtl*>(ctl);
@@ -413,12 +417,23 @@ int itb_self_attention(int dtype, const itb_ctl* ctl, const int* sent_done, cons
 int itb_cross_attention(int dtype, const itb_ctl* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
                         const void* cross_kv, int layer, const unsigned char* src_mask, void* ctx, int M, int beam, int d,
                         int H, int S, int L, void* stream) {
+    return itb_cross_attention_impl(dtype, ctl, sent_done, mem_len, q, ldq, cross_kv, layer, src_mask, ctx, M, beam, d, H, S, L, 0, stream);
+}
+
+}  // extern "C"
+
+// early_kv != 0: the caller guarantees that cross_kv and src_mask were complete before the last FULL stream dependency
+// (the decoder: cross-KV GEMM -> init_state (plain launch) -> steps), so the kernel may fetch them ahead of its
+// programmatic-dependency wait.  The public entry point cannot know that and passes 0.
+int itb_cross_attention_impl(int dtype, const itb_ctl* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
+                             const void* cross_kv, int layer, const unsigned char* src_mask, void* ctx, int M, int beam, int d,
+                             int H, int S, int L, int early_kv, void* stream) {
     ITB_REQUIRE(d == H * DH, "cross_attention: head_dim must be 64 (d == 64*H)");
     ITB_REQUIRE(S <= 2048, "cross_attention: S too large for the shared-memory score buffer");
     ITB_REQUIRE(M % beam == 0, "cross_attention: M must be a multiple of the beam width");
     if (use_mma(dtype))
         return itb_attn_mma(dtype, false, ctl, sent_done, mem_len, q, ldq, const_cast<void*>(cross_kv), nullptr, src_mask, ctx, M, beam, d,
-                            0, S, L, layer, (cudaStream_t)stream);
+                            0, S, L, layer, early_kv, (cudaStream_t)stream);
     AttnArgs a = {};
     a.ctl = reinterpret_cast<const ItbCtl*>(ctl);
     a.sent_done = sent_done; a.mem_len = mem_len;
@@ -429,4 +444,4 @@ int itb_cross_attention(int dtype, const itb_ctl* ctl, const int* sent_done, con
     return launch_cross<float>(a, H, (cudaStream_t)stream);
 }
 
-}  // extern "C"
+

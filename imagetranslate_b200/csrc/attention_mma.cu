@@ -39,6 +39,7 @@ struct AttnMmaArgs {
     const ItbCtl* ctl;
     const int* sent_done;                // [B] or null
     const int* mem_len;                  // cross: [B] or null (= S)
+    int early_kv;                        // cross: K,V and mask were complete before the last full stream dependency
     const float* q; int ldq;             // f32 queries (self: qkv buffer, k at +d, v at +2d)
     void* kv;                            // self: [M][T_max][2][d]; cross: [B][S][L][2][d]
     const unsigned char* anc;            // self: [2][M][T_max]
@@ -84,7 +85,6 @@ __device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t&
 template <typename T, bool SELF>
 __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaArgs a) {
     pdl_trigger();
-    pdl_wait();
     const int lane = threadIdx.x & 31, nl = lane >> 2, c = lane & 3;       // nl: B-fragment column / C row; c: quad lane
     const int wg = blockIdx.x * AM_WARPS + (threadIdx.x >> 5);
     if (wg >= a.n_warps) return;
@@ -92,6 +92,42 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
     const int h = wg % H, z = (wg / H) % nz, b = wg / (H * nz);
     const int q0 = z * 4, row0 = b * a.beam + q0, nq = min(4, a.beam - q0);
     const int hoff = h * DH;
+    // Per-warp staging buffer: AM_STAGE virtual rows of [K 128 B | V 128 B], padded to 272 B so that the fragment reads
+    // below are bank-conflict free.  All rows of a stage are requested with cp.async (16 B each, zero-filled when the
+    // virtual position does not exist) BEFORE anything is consumed: one memory round trip per 64 positions, no
+    // registers tied up by loads in flight.
+    extern __shared__ __align__(16) unsigned char am_smem[];
+    unsigned char* ws = am_smem + (size_t)(threadIdx.x >> 5) * (AM_STAGE * AM_ROWB);
+    const uint32_t ws_u32 = (uint32_t)__cvta_generic_to_shared(ws);
+    const int part = lane & 15;                                     // 16-byte piece of the 256-byte row this lane copies
+    const size_t part_off = (part < 8) ? (size_t)part * 8 : (size_t)d + (size_t)(part - 8) * 8;
+    // Cross-attention: the encoder-side K,V and the source mask were written once per batch, many launches ago, and
+    // their addresses depend on the warp index only.  The first stage is therefore requested BEFORE the wait on the
+    // predecessor grid and before the control words are known (rows past the source length are fetched too and
+    // masked below; rows past S are zero-filled) -- it overlaps the tail of the previous kernel and the query loads.
+    int mk0[AM_NCH];
+    if (SELF || a.early_kv == 0) pdl_wait();
+    if (!SELF) {
+        const T* cbase = reinterpret_cast<const T*>(a.kv) + ((size_t)b * a.S * a.L + a.layer) * 2 * d + hoff;
+        const size_t cstride = (size_t)a.L * 2 * d;
+#pragma unroll
+        for (int k = 0; k < AM_STAGE / 2; ++k) {
+            const int row = 2 * k + (lane >> 4);
+            if ((row & ~31) < a.S) {
+                const bool ok = row < a.S;
+                const T* src = cbase + (ok ? (size_t)row * cstride + part_off : (size_t)0);
+                const uint32_t dst = ws_u32 + row * AM_ROWB + part * 16;
+                const int nbytes = ok ? 16 : 0;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nbytes) : "memory");
+            }
+        }
+#pragma unroll
+        for (int hv = 0; hv < AM_NCH; ++hv) {
+            const int v = 32 * hv + lane;
+            mk0[hv] = (a.mask != nullptr && v < a.S) ? (int)a.mask[(size_t)b * a.S + v] : 1;
+        }
+        if (a.early_kv != 0) pdl_wait();
+    }
     // ---- first round trip: everything whose address depends on the warp index only (control words, the query row,
     //      the row's new K,V) is requested before anything is consumed ----
     int4 c4 = make_int4(1, 0, 0, 0);                     // {step, done, steps_run, cur}
@@ -109,7 +145,20 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
             for (int i = 0; i < 4; ++i) { kx[i] = qp[d / 4 + i]; vx[i] = qp[d / 2 + i]; }
         }
     }
-    if (c4.y != 0 || sdone != 0) return;
+    // self: the ancestor bytes of positions [0,32) of the group's rows, for BOTH parities of the ancestor table (which
+    // one is current is in the control word that is still in flight) -- short contexts need no further table reads
+    int pa[2][4];
+    if (SELF) {
+#pragma unroll
+        for (int par = 0; par < 2; ++par)
+#pragma unroll
+            for (int qi = 0; qi < 4; ++qi)
+                pa[par][qi] = (lane < a.T_max) ? (int)a.anc[((size_t)par * a.M + row0 + min(qi, nq - 1)) * a.T_max + lane] : 0;
+    }
+    if (c4.y != 0 || sdone != 0) {
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        return;
+    }
     if (SELF) n = c4.x;                                  // self: positions 0..step-1
 
     // ---- Q fragments.  A-operand quad of k-slice ks = {a0: row nl, k 0-7 | a1: row nl+8, k 0-7 | a2: row nl, k 8-15 |
@@ -132,6 +181,7 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
     size_t pos_stride;                   // elements between consecutive row indices
     int cshared = n, tl = 0, nv = n;     // self: [0,cshared) shared, then nq tails of tl positions each
     const unsigned char* anc0 = nullptr;
+    int a0b[4] = {0, 0, 0, 0};           // self: ancestor slot of position `lane` for the group's 4 rows (current parity)
     if (SELF) {
         const int pc = n - 1;
         base = reinterpret_cast<const T*>(a.kv) + hoff;
@@ -151,14 +201,20 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
             reinterpret_cast<uint4*>(dst + d)[1] = make_uint4(w[4], w[5], w[6], w[7]);
         }
         // first position whose physical row differs between the group's slots
+#pragma unroll
+        for (int qi = 0; qi < 4; ++qi) a0b[qi] = (c4.w != 0) ? pa[1][qi] : pa[0][qi];
         cshared = pc;
         if (nq > 1) {
             for (int blk = 0; blk * 32 < pc; ++blk) {
                 const int p = blk * 32 + lane;
                 bool same = true;
                 if (p < pc) {
-                    const int a0 = anc0[p];
-                    for (int qi = 1; qi < nq; ++qi) same = same && (anc0[(size_t)qi * a.T_max + p] == a0);
+                    if (blk == 0) {
+                        same = (a0b[1] == a0b[0]) && (a0b[2] == a0b[0]) && (a0b[3] == a0b[0]);   // rows >= nq mirror row nq-1
+                    } else {
+                        const int a0 = anc0[p];
+                        for (int qi = 1; qi < nq; ++qi) same = same && (anc0[(size_t)qi * a.T_max + p] == a0);
+                    }
                 }
                 const unsigned bal = __ballot_sync(0xffffffffu, !same);
                 if (bal != 0u) { cshared = blk * 32 + __ffs(bal) - 1; break; }
@@ -179,16 +235,6 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
     float m_run = -INFINITY, l_run = 0.f;
     const int qrow = nl & 3;             // rows 4..7 mirror rows 0..3 (their results are discarded)
 
-    // Per-warp staging buffer: AM_STAGE virtual rows of [K 128 B | V 128 B], padded to 272 B so that the fragment reads
-    // below are bank-conflict free.  All rows of a stage are requested with cp.async (16 B each, zero-filled when the
-    // virtual position does not exist) BEFORE anything is consumed: one memory round trip per 64 positions, no
-    // registers tied up by loads in flight.
-    extern __shared__ __align__(16) unsigned char am_smem[];
-    unsigned char* ws = am_smem + (size_t)(threadIdx.x >> 5) * (AM_STAGE * AM_ROWB);
-    const uint32_t ws_u32 = (uint32_t)__cvta_generic_to_shared(ws);
-    const int part = lane & 15;                                     // 16-byte piece of the 256-byte row this lane copies
-    const size_t part_off = (part < 8) ? (size_t)part * 8 : (size_t)d + (size_t)(part - 8) * 8;
-
     for (int sb = 0; sb < nv; sb += AM_STAGE) {
         // ---- virtual positions sb + 32*hv + lane: row index and meta = owner mask (bits 0-3) | masked-source (bit 4) ----
         int rowidx[AM_NCH], meta[AM_NCH];
@@ -196,27 +242,30 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
         for (int hv = 0; hv < AM_NCH; ++hv) {
             rowidx[hv] = -1; meta[hv] = 0;
             const int v = sb + 32 * hv + lane;
-            if (v < nv) {
-                if (SELF) {
-                    if (v < cshared) { rowidx[hv] = (b * a.beam + anc0[v]) * a.T_max + v; meta[hv] = 0xF; }
-                    else {
-                        const int vt = v - cshared;
-                        const int qi = (vt >= tl) + (vt >= 2 * tl) + (vt >= 3 * tl);
-                        const int p = cshared + vt - qi * tl;
-                        const int slot = (p == n - 1) ? (q0 + qi) : anc0[(size_t)qi * a.T_max + p];
-                        rowidx[hv] = (b * a.beam + slot) * a.T_max + p;
-                        meta[hv] = 1 << qi;
-                    }
-                } else {
+            if (SELF) {
+                const bool in = v < nv, tail = in && v >= cshared;
+                const int vt = v - cshared;
+                const int qi = tail ? (vt >= tl) + (vt >= 2 * tl) + (vt >= 3 * tl) : 0;
+                const int p = tail ? cshared + vt - qi * tl : v;                 // cache position of this virtual position
+                // ancestor slot of (row qi, position p): in registers for p < 32, in the table above that
+                const int s0 = __shfl_sync(0xffffffffu, a0b[0], p & 31), s1 = __shfl_sync(0xffffffffu, a0b[1], p & 31);
+                const int s2 = __shfl_sync(0xffffffffu, a0b[2], p & 31), s3 = __shfl_sync(0xffffffffu, a0b[3], p & 31);
+                int slot = (qi == 0) ? s0 : (qi == 1) ? s1 : (qi == 2) ? s2 : s3;
+                if (in && p >= 32) slot = anc0[(size_t)qi * a.T_max + p];
+                if (tail && p == n - 1) slot = q0 + qi;                          // the row appended above
+                if (in) { rowidx[hv] = (b * a.beam + slot) * a.T_max + p; meta[hv] = tail ? (1 << qi) : 0xF; }
+            } else if (v < nv) {
+                {
                     rowidx[hv] = v;
-                    meta[hv] = 0xF | ((mrow != nullptr && mrow[v] == 0) ? 0x10 : 0);
+                    const int mk = (sb == 0) ? mk0[hv] : ((mrow != nullptr) ? (int)mrow[v] : 1);
+                    meta[hv] = 0xF | ((mk == 0) ? 0x10 : 0);
                 }
             }
         }
         const int nchunk = min(AM_NCH, (nv - sb + 31) >> 5);         // 32-position chunks in this stage (warp-uniform)
 #pragma unroll
         for (int k = 0; k < AM_STAGE / 2; ++k) {
-            if (k < 16 * nchunk) {
+            if (k < 16 * nchunk && (SELF || sb != 0)) {              // cross: stage 0 was requested at the top
                 const int row = 2 * k + (lane >> 4);
                 const int r = __shfl_sync(0xffffffffu, rowidx[k >> 4], row & 31);
                 const T* src = base + ((r >= 0) ? (size_t)r * pos_stride + part_off : (size_t)0);
@@ -337,8 +386,9 @@ static int launch_attn_mma(AttnMmaArgs a, bool self, cudaStream_t s) {
 // Called by itb_self_attention / itb_cross_attention (attention.cu) for the 16-bit dtypes.
 int itb_attn_mma(int dtype, bool self, const void* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
                  void* kv, const unsigned char* anc, const unsigned char* mask, void* ctx, int M, int beam, int d, int T_max,
-                 int S, int L, int layer, cudaStream_t s) {
+                 int S, int L, int layer, int early_kv, cudaStream_t s) {
     AttnMmaArgs a = {};
+    a.early_kv = early_kv;
     a.ctl = reinterpret_cast<const ItbCtl*>(ctl);
     a.sent_done = sent_done; a.mem_len = mem_len; a.q = q; a.ldq = ldq; a.kv = kv; a.anc = anc; a.mask = mask; a.ctx = ctx;
     a.M = M; a.beam = beam; a.d = d; a.T_max = T_max; a.S = S; a.L = L; a.layer = layer;

@@ -66,6 +66,41 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accum) : "memory");
 }
+// ---- CTA-pair (cta_group::2) variants: the two CTAs of a cluster on one TPC run ONE 256-row MMA; each stages its own
+//      128 UMMA-A rows and HALF of the UMMA-B rows, so a CTA pulls 32 KB instead of 48 KB through L2 per k-block ----
+__device__ __forceinline__ uint32_t cluster_addr_of(uint32_t smem_addr, uint32_t cta_rank) {   // same offset, CTA `cta_rank`
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(cta_rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar_addr) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA load into THIS CTA's shared memory whose byte count is credited to the barrier at `cluster_bar_addr` (the leader's)
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint32_t cluster_bar_addr) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(cluster_bar_addr), "r"(c0), "r"(c1)
+        : "memory");
+}
+// arrives on the barrier at this shared-memory offset in BOTH CTAs of the pair once the MMAs issued so far retire
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+    asm volatile(
+        "{\n\t.reg .b16 m;\n\tmov.b16 m, 3;\n\t"
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m;\n\t}"
+        ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accum) : "memory");
+}
 // K-major, SWIZZLE_128B shared-memory matrix descriptor (sm_100 format: version=1 at bit 46, layout type 2 at bit 61).
 // Rows are 128 bytes; 8-row groups are 1024 bytes apart (SBO); LBO unused for swizzled K-major.
 __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
@@ -132,17 +167,22 @@ struct TcVocabPart {
 // epilogue thread owns ONE decoder row and walks its 128 logits of the tile in registers: + bias, running max / sum-exp
 // (EX2 with pre-scaled argument), sorted top-KT insertion (strict >, ascending index => lowest index wins ties).
 // Warps 4-7 take columns [0,128), warps 8-11 columns [128,256) of the tile; chunk index = 2 * vocab tile + half.
-template <int MT, int KT>
+// PAIR: the 2-CTA launch (gemm_tc2_vocab_kernel): tiles are walked per CTA pair, this CTA owns row tile 2 * (pair's row
+// tile) + rank, and the "accumulator drained" arrival goes to the LEADER CTA's barrier (tempty_remote = its
+// shared::cluster address).
+template <int MT, int KT, bool PAIR = false>
 __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty, const float* __restrict__ bias,
                                                   const TcVocabPart vp, int V, int rows, int total, int m_tiles, int n_tiles,
-                                                  int warp, int lane) {
+                                                  int warp, int lane, uint32_t tempty_remote = 0u) {
     static_assert(MT == 256, "the vocabulary epilogue is written for 256-entry tiles");
     constexpr float kLog2e = 1.4426950408889634f;
     const int q = warp & 3, half = (warp - 4) >> 2;
     uint32_t as = 0, aphase = 0;
-    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+    const int t0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, tstep = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    for (int t = t0; t < total; t += tstep) {
         int ks, mt, nt;
         tc_tile_of<true>(t, 1, m_tiles, n_tiles, ks, mt, nt);
+        if (PAIR) nt = 2 * nt + (int)(blockIdx.x & 1);
         mbar_wait(&tfull[as], aphase);
         tc_fence_after();
         const int r = nt * TC_BN + q * 32 + lane;                   // decoder row of this thread
@@ -220,7 +260,8 @@ __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* 
             }
         }
         tc_fence_before();
-        mbar_arrive(&tempty[as]);
+        if (PAIR) mbar_arrive_cluster(tempty_remote + 8u * as);
+        else mbar_arrive(&tempty[as]);
         if (++as == 2) { as = 0; aphase ^= 1; }
     }
 }
@@ -409,6 +450,137 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
     }
 }
 
+// ---------------------------------- fused vocabulary projection on CTA pairs ----------------------------------
+// Same math and output as gemm_tc_kernel<256, ITB_EPI_VOCAB_*>, but ONE tile (256 decoder rows x 256 vocabulary entries)
+// per CTA PAIR: tcgen05.mma.cta_group::2 with M = 256.  Each CTA stages its own 128 decoder rows and 128 of the tile's
+// 256 vocabulary rows per k-block (32 KB instead of 48 KB per 128x256x64 MACs), which is what the single-CTA launch is
+// bound by (L2 -> SM operand feed).  The leader CTA (rank 0) owns the "stage full" and "accumulator drained" barriers
+// and issues the MMAs; "stage free" and "accumulator ready" are multicast to both CTAs by tcgen05.commit.
+#define TC2_HALF_BYTES (128 * TC_BK * 2)          // one 128-row operand tile of a stage (16 KB)
+#define TC2_STAGES 6
+#define TC2_SMEM (TC2_STAGES * 2 * TC2_HALF_BYTES + 1024 + 256)
+
+template <int KT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
+gemm_tc2_vocab_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmWv,
+                      const ItbCtl* __restrict__ ctl, const float* __restrict__ bias, int V, int rows, int K, int act_f16,
+                      const TcVocabPart vp) {
+    extern __shared__ uint8_t smem_raw[];
+    pdl_trigger();
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem_x = smem;                                           // [stages][128 decoder rows][64]
+    uint8_t* smem_w = smem + TC2_STAGES * TC2_HALF_BYTES;             // [stages][128 vocabulary rows][64]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TC2_STAGES * 2 * TC2_HALF_BYTES);
+    uint64_t* full = bars;                     // leader's is used: expects both CTAs' bytes
+    uint64_t* empty = bars + TC2_STAGES;       // per CTA, multicast arrival
+    uint64_t* tfull = bars + 2 * TC2_STAGES;   // per CTA, multicast arrival
+    uint64_t* tempty = tfull + 2;              // leader's is used: 256 epilogue threads of each CTA
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    const int pair = blockIdx.x >> 1, npair = gridDim.x >> 1;
+    const int rp_tiles = (rows + 255) / 256, v_tiles = (V + 255) / 256, total = rp_tiles * v_tiles, KB = K / TC_BK;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmX)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmWv)) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < TC2_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 512); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    cluster_sync_all();                        // both CTAs' barriers exist before any remote arrival / TMEM pairing
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t full_l = cluster_addr_of(smem_u32(full), 0), tempty_l = cluster_addr_of(smem_u32(tempty), 0);
+
+    // the weight halves of the first stages are requested before the programmatic-dependency wait (weights are static)
+    int pre = 0;
+    if (warp == 0 && lane == 0 && pair < total) {
+        const int vt = pair / rp_tiles;
+        pre = KB < TC2_STAGES ? KB : TC2_STAGES;
+        for (int kb = 0; kb < pre; ++kb) {
+            if (rank == 0) mbar_expect_tx(&full[kb], 4 * TC2_HALF_BYTES);
+            tma_load_2d_pair(smem_w + kb * TC2_HALF_BYTES, &tmWv, kb * TC_BK, vt * 256 + (int)rank * 128, full_l + 8u * kb);
+        }
+    }
+    pdl_wait();
+    const bool done = (ctl != nullptr) && (ctl->done != 0);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            if (pair < total) {
+                const int rp = pair % rp_tiles;
+                for (int kb = 0; kb < pre; ++kb)
+                    tma_load_2d_pair(smem_x + kb * TC2_HALF_BYTES, &tmX, kb * TC_BK, (2 * rp + (int)rank) * 128, full_l + 8u * kb);
+                if (done && rank == 0)                 // search already terminated: drain both CTAs' copies, then leave
+                    for (int kb = 0; kb < pre; ++kb) mbar_wait(&full[kb], 0);
+            }
+            if (!done) {
+                uint32_t stage = (pre == TC2_STAGES) ? 0 : pre, phase = (pre == TC2_STAGES) ? 1 : 0;
+                int kb0 = pre;
+                for (int t = pair; t < total; t += npair) {
+                    const int rp = t % rp_tiles, vt = t / rp_tiles;
+                    for (int kb = kb0; kb < KB; ++kb) {
+                        mbar_wait(&empty[stage], phase ^ 1);
+                        if (rank == 0) mbar_expect_tx(&full[stage], 4 * TC2_HALF_BYTES);
+                        tma_load_2d_pair(smem_w + stage * TC2_HALF_BYTES, &tmWv, kb * TC_BK, vt * 256 + (int)rank * 128, full_l + 8u * stage);
+                        tma_load_2d_pair(smem_x + stage * TC2_HALF_BYTES, &tmX, kb * TC_BK, (2 * rp + (int)rank) * 128, full_l + 8u * stage);
+                        if (++stage == TC2_STAGES) { stage = 0; phase ^= 1; }
+                    }
+                    kb0 = 0;
+                }
+            }
+        }
+    } else if (done) {
+        // nothing to compute
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            // D = f32; A, B formats equal (bf16 = 1 / f16 = 0); both K-major; N = 256 (>>3 @17); M = 256 over the pair (>>4 @24)
+            const uint32_t idesc = (1u << 4) | ((act_f16 ? 0u : 1u) << 7) | ((act_f16 ? 0u : 1u) << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+            uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+            for (int t = pair; t < total; t += npair) {
+                mbar_wait(&tempty[as], aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * 256;
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint64_t dx = make_sw128_desc(smem_u32(smem_x + stage * TC2_HALF_BYTES));
+                    const uint64_t dw = make_sw128_desc(smem_u32(smem_w + stage * TC2_HALF_BYTES));
+#pragma unroll
+                    for (int k = 0; k < TC_BK / 16; ++k)
+                        umma_bf16_pair(d_tmem, dx + 2 * k, dw + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                    umma_commit_pair(&empty[stage]);
+                    if (++stage == TC2_STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_pair(&tfull[as]);
+                if (++as == 2) { as = 0; aphase ^= 1; }
+            }
+        }
+    } else if (warp >= 4) {
+        tc_epilogue_vocab<256, KT, true>(tmem_base, tfull, tempty, bias, vp, V, rows, total, v_tiles, rp_tiles, warp, lane, tempty_l);
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                        // the peer's shared memory / barriers stay alive until both CTAs are through
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
 // ------------------------------------------------ host side ------------------------------------------------
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -523,17 +695,53 @@ int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const v
     }
 }
 
-// Fused vocabulary projection (operands swapped: tmX = activations [rows][K] box 128, tmWv = weights [V][K] box 256).
+// Fused vocabulary projection (operands swapped: tmX = activations [rows][K] box 128, tmWv = weights [V][K] box 256,
+// tmWv128 = the same weights with a 128-row box for the CTA-pair launch, or null).
 // Writes per (row, 128-entry chunk) max / sum-exp / top-KT into vp; n_chunk must be itb_vocab_chunks(V).
-int itb_gemm_tc_vocab(int kt, const CUtensorMap* tmX, const CUtensorMap* tmWv, const void* ctl, const float* bias, int rows, int V,
-                      int K, int act_f16, float* cand_val, int* cand_idx, float* chunk_max, float* chunk_sum, float* logits,
-                      int ldl, int n_chunk, cudaStream_t s) {
+template <int KT>
+static int launch_tc2_vocab(const CUtensorMap& tmX, const CUtensorMap& tmWv128, const ItbCtl* ctl, const float* bias, int rows, int V,
+                            int K, int act_f16, cudaStream_t s, const TcVocabPart& vp) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc2_vocab_kernel<KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM);
+        if (e != cudaSuccess) { itb_set_error("gemm_tc2: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return -1; }
+        attr_set = true;
+    }
+    const int total = ((rows + 255) / 256) * ((V + 255) / 256);
+    const int cap = num_sms() & ~1;
+    const int grid = 2 * total < cap ? 2 * total : cap;
+    cudaError_t e = itb_launch(gemm_tc2_vocab_kernel<KT>, dim3(grid), dim3(TC_THREADS), (size_t)TC2_SMEM, s, tmX, tmWv128, ctl, bias, V,
+                               rows, K, act_f16, vp);
+    if (e != cudaSuccess) { itb_set_error("gemm_tc2: launch failed: %s", cudaGetErrorString(e)); return -1; }
+    return itb_check_launch("gemm_tc2");
+}
+
+// CTA-pair launch (needs at least two 128-row tiles of decoder rows): opt-in with ITB_VOCAB_PAIR=1 -- measured 1% SLOWER
+// than the single-CTA launch at 4096 rows, because the launch is bound by the epilogue's instruction issue, not by
+// the operand feed the pairing halves.
+static bool use_pair(int rows) {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("ITB_VOCAB_PAIR");
+        v = (e != nullptr && e[0] == '1') ? 1 : 0;
+    }
+    return v != 0 && rows > 128;
+}
+
+int itb_gemm_tc_vocab(int kt, const CUtensorMap* tmX, const CUtensorMap* tmWv, const CUtensorMap* tmWv128, const void* ctl,
+                      const float* bias, int rows, int V, int K, int act_f16, float* cand_val, int* cand_idx, float* chunk_max,
+                      float* chunk_sum, float* logits, int ldl, int n_chunk, cudaStream_t s) {
     ITB_REQUIRE(K % TC_BK == 0 && K >= TC_BK, "vocab(tcgen05): K must be a multiple of 64");
     ITB_REQUIRE(n_chunk == 2 * ((V + 255) / 256), "vocab(tcgen05): n_chunk must be 2 * ceil(V / 256)");
     TcVocabPart vp;
     vp.cand_val = cand_val; vp.cand_idx = cand_idx; vp.chunk_max = chunk_max; vp.chunk_sum = chunk_sum;
     vp.logits = logits; vp.ldl = ldl; vp.n_chunk = n_chunk;
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
+    if (tmWv128 != nullptr && use_pair(rows)) {
+        if (kt == 4) return launch_tc2_vocab<4>(*tmX, *tmWv128, c, bias, rows, V, K, act_f16, s, vp);
+        if (kt == 8) return launch_tc2_vocab<8>(*tmX, *tmWv128, c, bias, rows, V, K, act_f16, s, vp);
+        return launch_tc2_vocab<16>(*tmX, *tmWv128, c, bias, rows, V, K, act_f16, s, vp);
+    }
     // kernel view: the 128-row operand ("N") is the activation matrix, the 256-row operand ("M") the weights
     if (kt == 4) return launch_tc<256, ITB_EPI_VOCAB_K4>(*tmX, *tmWv, c, bias, nullptr, V, rows, K, 0, act_f16, 1, s, vp);
     if (kt == 8) return launch_tc<256, ITB_EPI_VOCAB_K8>(*tmX, *tmWv, c, bias, nullptr, V, rows, K, 0, act_f16, 1, s, vp);
