@@ -167,16 +167,39 @@ struct TcVocabPart {
 // epilogue thread owns ONE decoder row and walks its 128 logits of the tile in registers: + bias, running max / sum-exp
 // (EX2 with pre-scaled argument), sorted top-KT insertion (strict >, ascending index => lowest index wins ties).
 // Warps 4-7 take columns [0,128), warps 8-11 columns [128,256) of the tile; chunk index = 2 * vocab tile + half.
+#define TC_CAND 16          // candidate slots per epilogue thread (KT = 4 path): [TC_CAND][256] floats = 16 KB per CTA
+// logits of 32 consecutive vocabulary entries from v0: accumulator + bias; entries past V read as -inf
+__device__ __forceinline__ void tc_vocab_bias(const uint32_t* v, float* x, const float* __restrict__ bias, int v0, int V) {
+    if (v0 + 32 <= V) {                                             // whole chunk inside the vocabulary: no per-entry checks
+        const float4* bp = reinterpret_cast<const float4*>(bias + v0);                   // same address in every lane
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 b4 = __ldg(bp + j4);
+            x[4 * j4] = __uint_as_float(v[4 * j4]) + b4.x;
+            x[4 * j4 + 1] = __uint_as_float(v[4 * j4 + 1]) + b4.y;
+            x[4 * j4 + 2] = __uint_as_float(v[4 * j4 + 2]) + b4.z;
+            x[4 * j4 + 3] = __uint_as_float(v[4 * j4 + 3]) + b4.w;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const bool ok = v0 + j < V;
+            x[j] = ok ? __uint_as_float(v[j]) + __ldg(bias + (ok ? v0 + j : 0)) : -INFINITY;
+        }
+    }
+}
+
 // PAIR: the 2-CTA launch (gemm_tc2_vocab_kernel): tiles are walked per CTA pair, this CTA owns row tile 2 * (pair's row
 // tile) + rank, and the "accumulator drained" arrival goes to the LEADER CTA's barrier (tempty_remote = its
 // shared::cluster address).
 template <int MT, int KT, bool PAIR = false>
 __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty, const float* __restrict__ bias,
                                                   const TcVocabPart vp, int V, int rows, int total, int m_tiles, int n_tiles,
-                                                  int warp, int lane, uint32_t tempty_remote = 0u) {
+                                                  int warp, int lane, float* cbuf, uint32_t tempty_remote = 0u) {
     static_assert(MT == 256, "the vocabulary epilogue is written for 256-entry tiles");
     constexpr float kLog2e = 1.4426950408889634f;
     const int q = warp & 3, half = (warp - 4) >> 2;
+    float* const cslot = cbuf + (threadIdx.x - 128);                // candidate values of this thread: cslot[k * 256]
     uint32_t as = 0, aphase = 0;
     const int t0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, tstep = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
     for (int t = t0; t < total; t += tstep) {
@@ -192,8 +215,102 @@ __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* 
 #pragma unroll
             for (int j = 0; j < KT; ++j) { tv[j] = -INFINITY; ti[j] = -1; }
             float m = -INFINITY, s = 0.f;
+            bool scan_all = true;                                   // top-KT by walking every entry (the KT > 4 path)
+            if constexpr (KT == 4) {
+                // ---- KT = 4: two passes, so that the data-dependent insertion runs over ~6 candidates per row
+                //      instead of being dragged through all 128 entries by whichever lane of the warp inserts ----
+                const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + as * MT + half * 128;
+                // pass 1: log-sum-exp statistics and the maxima of the 8 groups of 16 entries
+                float gm[8];
+#pragma unroll
+                for (int ci = 0; ci < 4; ++ci) {
+                    const int v0 = vbase + 32 * ci;
+                    gm[2 * ci] = -INFINITY; gm[2 * ci + 1] = -INFINITY;
+                    if (v0 < V) {
+                        uint32_t v[32];
+                        tmem_ld32(tcol + 32 * ci, v);
+                        float x[32];
+                        tc_vocab_bias(v, x, bias, v0, V);
+                        if (vp.logits != nullptr && r < rows) {
+                            float* lp = vp.logits + (size_t)r * vp.ldl + v0;
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) if (v0 + j < V) lp[j] = x[j];
+                        }
+                        float g0 = x[0], g1 = x[16];
+#pragma unroll
+                        for (int j = 1; j < 16; ++j) { g0 = fmaxf(g0, x[j]); g1 = fmaxf(g1, x[16 + j]); }
+                        gm[2 * ci] = g0; gm[2 * ci + 1] = g1;
+                        const float bm = fmaxf(g0, g1);
+                        if (bm > m) {
+                            s = (m == -INFINITY) ? 0.f : s * tc_ex2((m - bm) * kLog2e);
+                            m = bm;
+                        }
+                        const float nm = -m * kLog2e;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) s += tc_ex2(fmaf(x[j], kLog2e, nm));   // padding: ex2(-inf) = 0
+                    }
+                }
+                // T = 4th largest group maximum: four distinct entries are >= T, so every top-4 entry is >= T
+                float t0 = -INFINITY, t1 = -INFINITY, t2 = -INFINITY, t3 = -INFINITY;
+#pragma unroll
+                for (int g = 0; g < 8; ++g) {
+                    float cgm = gm[g], hi;
+                    hi = fmaxf(t0, cgm); cgm = fminf(t0, cgm); t0 = hi;
+                    hi = fmaxf(t1, cgm); cgm = fminf(t1, cgm); t1 = hi;
+                    hi = fmaxf(t2, cgm); cgm = fminf(t2, cgm); t2 = hi;
+                    t3 = fmaxf(t3, cgm);
+                }
+                // pass 2: entries >= T go to this thread's column of the candidate buffer (ring of TC_CAND slots), their
+                // positions into one bit mask per 32 entries
+                uint32_t mk[4] = {0u, 0u, 0u, 0u};
+                uint32_t wofs = 0u;
+#pragma unroll
+                for (int ci = 0; ci < 4; ++ci) {
+                    const int v0 = vbase + 32 * ci;
+                    if (v0 < V) {
+                        uint32_t v[32];
+                        tmem_ld32(tcol + 32 * ci, v);
+                        float x[32];
+                        tc_vocab_bias(v, x, bias, v0, V);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            if (x[j] >= t3 && x[j] > -INFINITY) {
+                                cslot[wofs] = x[j];
+                                wofs = (wofs + 256u) & (TC_CAND * 256u - 1u);
+                                mk[ci] |= 1u << j;
+                            }
+                        }
+                    }
+                }
+                const int ncand = __popc(mk[0]) + __popc(mk[1]) + __popc(mk[2]) + __popc(mk[3]);
+                // ring overflowed in some lane (many equal logits; practically never): the whole warp walks everything --
+                // warp-uniform, because the walk below re-reads TMEM with .sync.aligned loads
+                scan_all = __any_sync(0xffffffffu, ncand > TC_CAND);
+                if (!scan_all) {
+                    // pass 3: sorted insertion of the candidates, ascending index (strict > keeps the lowest index first)
+                    uint32_t cur = mk[0];
+                    int ci = 0;
+                    for (int k = 0; k < ncand; ++k) {
+                        while (cur == 0u) { ++ci; cur = (ci == 1) ? mk[1] : (ci == 2) ? mk[2] : mk[3]; }
+                        const int j = __ffs(cur) - 1;
+                        cur &= cur - 1u;
+                        const float xv = cslot[k * 256];
+                        if (xv > tv[3]) {
+                            tv[3] = xv; ti[3] = vbase + 32 * ci + j;
+#pragma unroll
+                            for (int u = 3; u > 0; --u) {
+                                if (tv[u] > tv[u - 1]) {
+                                    const float fv = tv[u]; tv[u] = tv[u - 1]; tv[u - 1] = fv;
+                                    const int fi = ti[u]; ti[u] = ti[u - 1]; ti[u - 1] = fi;
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            const bool stats = (KT != 4);                           // the KT = 4 path already has m, s and the logits
 #pragma unroll 1
-            for (int c0 = 0; c0 < 128; c0 += 32) {
+            for (int c0 = 0; c0 < (scan_all ? 128 : 0); c0 += 32) {
                 const int v0 = vbase + c0;
                 if (v0 >= V) break;                                 // entries past V: the chunk stays (or ends) empty
                 uint32_t v[32];
@@ -220,18 +337,20 @@ __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* 
                         bm = fmaxf(bm, x[j]);
                     }
                 }
-                if (vp.logits != nullptr && r < rows) {
-                    float* lp = vp.logits + (size_t)r * vp.ldl + v0;
+                if (stats) {
+                    if (vp.logits != nullptr && r < rows) {
+                        float* lp = vp.logits + (size_t)r * vp.ldl + v0;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) if (v0 + j < V) lp[j] = x[j];
-                }
-                if (bm > m) {
-                    s = (m == -INFINITY) ? 0.f : s * tc_ex2((m - bm) * kLog2e);
-                    m = bm;
-                }
-                const float nm = -m * kLog2e;
+                        for (int j = 0; j < 32; ++j) if (v0 + j < V) lp[j] = x[j];
+                    }
+                    if (bm > m) {
+                        s = (m == -INFINITY) ? 0.f : s * tc_ex2((m - bm) * kLog2e);
+                        m = bm;
+                    }
+                    const float nm = -m * kLog2e;
 #pragma unroll
-                for (int j = 0; j < 32; ++j) s += tc_ex2(fmaf(x[j], kLog2e, nm));       // padding: ex2(-inf) = 0
+                    for (int j = 0; j < 32; ++j) s += tc_ex2(fmaf(x[j], kLog2e, nm));   // padding: ex2(-inf) = 0
+                }
                 if (bm > tv[KT - 1]) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
@@ -337,6 +456,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
     uint64_t* tfull = bars + 2 * Cfg::kStages;
     uint64_t* tempty = tfull + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+    float* cbuf = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);   // vocabulary launches only (kVocabExtra)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_tiles = (N + TC_BN - 1) / TC_BN, m_tiles = (M + MT - 1) / MT;
@@ -434,9 +554,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
             }
         }
     } else if (warp >= 4) {
-        if constexpr (EPI == ITB_EPI_VOCAB_K4) tc_epilogue_vocab<MT, 4>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane);
-        else if constexpr (EPI == ITB_EPI_VOCAB_K8) tc_epilogue_vocab<MT, 8>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane);
-        else if constexpr (EPI == ITB_EPI_VOCAB_K16) tc_epilogue_vocab<MT, 16>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane);
+        if constexpr (EPI == ITB_EPI_VOCAB_K4) tc_epilogue_vocab<MT, 4>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane, cbuf);
+        else if constexpr (EPI == ITB_EPI_VOCAB_K8) tc_epilogue_vocab<MT, 8>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane, cbuf);
+        else if constexpr (EPI == ITB_EPI_VOCAB_K16) tc_epilogue_vocab<MT, 16>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane, cbuf);
         else if constexpr (EPI == ITB_EPI_BIAS_F32) tc_epilogue<MT, EPI, float>(tmem_base, tfull, tempty, bias, reinterpret_cast<float*>(out), M, N, ldo, nsplit, part_stride, total, m_tiles, warp, lane);
         else if (act_f16) tc_epilogue<MT, EPI, __half>(tmem_base, tfull, tempty, bias, reinterpret_cast<__half*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane);
         else tc_epilogue<MT, EPI, __nv_bfloat16>(tmem_base, tfull, tempty, bias, reinterpret_cast<__nv_bfloat16*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane);
@@ -458,7 +578,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
 // and issues the MMAs; "stage free" and "accumulator ready" are multicast to both CTAs by tcgen05.commit.
 #define TC2_HALF_BYTES (128 * TC_BK * 2)          // one 128-row operand tile of a stage (16 KB)
 #define TC2_STAGES 6
-#define TC2_SMEM (TC2_STAGES * 2 * TC2_HALF_BYTES + 1024 + 256)
+#define TC2_SMEM (TC2_STAGES * 2 * TC2_HALF_BYTES + 1024 + 256 + TC_CAND * 256 * 4)
 
 template <int KT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
@@ -476,6 +596,7 @@ gemm_tc2_vocab_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_cons
     uint64_t* tfull = bars + 2 * TC2_STAGES;   // per CTA, multicast arrival
     uint64_t* tempty = tfull + 2;              // leader's is used: 256 epilogue threads of each CTA
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+    float* cbuf = reinterpret_cast<float*>(smem + TC2_STAGES * 2 * TC2_HALF_BYTES + 256);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t rank;
@@ -569,7 +690,7 @@ gemm_tc2_vocab_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_cons
             }
         }
     } else if (warp >= 4) {
-        tc_epilogue_vocab<256, KT, true>(tmem_base, tfull, tempty, bias, vp, V, rows, total, v_tiles, rp_tiles, warp, lane, tempty_l);
+        tc_epilogue_vocab<256, KT, true>(tmem_base, tfull, tempty, bias, vp, V, rows, total, v_tiles, rp_tiles, warp, lane, cbuf, tempty_l);
     }
 
     tc_fence_before();
@@ -656,15 +777,16 @@ void itb_tc_plan(int M, int N, int K, int max_split, int* mt_out, int* split_out
 template <int MT, int EPI>
 static int launch_tc(const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCtl* ctl, const float* bias, void* out,
                      int M, int N, int K, int ldo, int act_f16, int nsplit, cudaStream_t s, const TcVocabPart vp = TcVocabPart()) {
+    constexpr int kSmem = TcCfg<MT>::kSmemBytes + (EPI >= ITB_EPI_VOCAB_K4 ? TC_CAND * 256 * 4 : 0);   // + candidate buffer
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<MT>::kSmemBytes);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
         if (e != cudaSuccess) { itb_set_error("gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return -1; }
         attr_set = true;
     }
     const int total = ((N + TC_BN - 1) / TC_BN) * ((M + MT - 1) / MT) * nsplit;
     const int grid = total < num_sms() ? total : num_sms();
-    cudaError_t e = itb_launch(gemm_tc_kernel<MT, EPI>, dim3(grid), dim3(TC_THREADS), (size_t)TcCfg<MT>::kSmemBytes, s, tmW, tmA,
+    cudaError_t e = itb_launch(gemm_tc_kernel<MT, EPI>, dim3(grid), dim3(TC_THREADS), (size_t)kSmem, s, tmW, tmA,
                                ctl, bias, out, M, N, K, ldo, act_f16, nsplit, (size_t)M * (size_t)ldo, vp);
     if (e != cudaSuccess) { itb_set_error("gemm_tc: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("gemm_tc");

@@ -103,6 +103,37 @@ def test_fused_vocab_projection_partials(dtype, rows, V, beam):
     assert torch.equal(tv, top.values)
 
 
+def test_fused_vocab_projection_equal_logits_take_the_lowest_indices():
+    """Rows whose logits are all equal (zero activations, zero bias) overflow the epilogue's candidate ring in some lanes
+    only: the warp must fall back to the full walk together, and ties must resolve to the lowest indices."""
+    lib, K, rows, V, beam = _lib.lib(), 768, 200, 1000, 4
+    x, w = _rand((rows, K), 41, 1.0, torch.bfloat16), _rand((V, K), 42, 0.05, torch.bfloat16)
+    x[5] = 0
+    x[77] = 0
+    x[131] = 0
+    b = torch.zeros(V, device=DEV)
+    nc, KT = lib.itb_vocab_chunks(V), lib.itb_topk_capacity(beam)
+    cand_val = torch.full((rows, nc, KT), float("nan"), device=DEV)
+    cand_idx = torch.full((rows, nc, KT), -7, dtype=torch.int32, device=DEV)
+    cmax, csum = torch.full((rows, nc), float("nan"), device=DEV), torch.full((rows, nc), float("nan"), device=DEV)
+    logits = torch.full((rows, (V + 3) // 4 * 4), float("nan"), device=DEV)
+    _lib.check(lib.itb_vocab_partials(_lib.BF16, beam, _lib.ptr(x), _lib.ptr(w), _lib.ptr(b), rows, V, K, _lib.ptr(cand_val),
+                                      _lib.ptr(cand_idx), _lib.ptr(cmax), _lib.ptr(csum), _lib.ptr(logits), stream()), "vocab_partials")
+    torch.cuda.synchronize()
+    got = logits[:, :V]
+    pad = torch.full((rows, nc * 128 - V), float("-inf"), device=DEV)
+    sl = torch.cat([got, pad], 1).view(rows, nc, 128)
+    order = torch.argsort(sl, dim=2, descending=True, stable=True)[:, :, :KT]
+    want_val = torch.gather(sl, 2, order)
+    want_idx = (order + (torch.arange(nc, device=DEV) * 128)[None, :, None]).to(torch.int32)
+    want_idx = torch.where(torch.isinf(want_val), torch.full_like(want_idx, -1), want_idx)
+    assert torch.equal(cand_val, want_val) and torch.equal(cand_idx, want_idx)
+    for r in (5, 77, 131):
+        assert torch.equal(got[r], torch.zeros(V, device=DEV))
+        assert cand_idx[r, 0].tolist() == [0, 1, 2, 3] and cand_idx[r, 3].tolist() == [384, 385, 386, 387]
+        assert torch.equal(csum[r, :7], torch.full((7,), 128.0, device=DEV))
+
+
 def test_linear_tcgen05_back_to_back_is_deterministic():
     A, W, b = _rand((244, 768), 7, 1.0, torch.bfloat16), _rand((3072, 768), 8, 0.05, torch.bfloat16), _rand((3072,), 9)
     o1 = linear(_lib.BF16, _lib.GEMM_TCGEN05, _lib.EPI_BIAS_F32, A, W, b)
