@@ -167,7 +167,12 @@ struct TcVocabPart {
 // epilogue thread owns ONE decoder row and walks its 128 logits of the tile in registers: + bias, running max / sum-exp
 // (EX2 with pre-scaled argument), sorted top-KT insertion (strict >, ascending index => lowest index wins ties).
 // Warps 4-7 take columns [0,128), warps 8-11 columns [128,256) of the tile; chunk index = 2 * vocab tile + half.
-#define TC_CAND 16          // candidate slots per epilogue thread (KT = 4 path): [TC_CAND][256] floats = 16 KB per CTA
+#define TC_VOC_EPI_WARPS 16 // epilogue warps of a vocabulary launch: 4 per TMEM lane quarter, 64 of the tile's 256 columns each
+#define TC_VOC_THREADS (128 + 32 * TC_VOC_EPI_WARPS)
+#define TC_CAND 12          // candidates per epilogue thread the KT = 4 path can take before it falls back to the full walk
+#define TC_CAND_SLOTS 16    // slots per thread: the write pointer is clamped once per 4 entries; [slots][512] floats = 32 KB per CTA
+#define TC_SLOT_STRIDE (32u * TC_VOC_EPI_WARPS * 4u)      // bytes between consecutive slots of one thread
+
 // logits of 32 consecutive vocabulary entries from v0: accumulator + bias; entries past V read as -inf
 __device__ __forceinline__ void tc_vocab_bias(const uint32_t* v, float* x, const float* __restrict__ bias, int v0, int V) {
     if (v0 + 32 <= V) {                                             // whole chunk inside the vocabulary: no per-entry checks
@@ -189,17 +194,247 @@ __device__ __forceinline__ void tc_vocab_bias(const uint32_t* v, float* x, const
     }
 }
 
+// sorted insertion, strict >: among equal values the one inserted first (the lower index) stays ahead
+template <int KT>
+__device__ __forceinline__ void tc_topk_insert(float (&tv)[KT], int (&ti)[KT], float xv, int idx) {
+    if (xv > tv[KT - 1]) {
+        tv[KT - 1] = xv; ti[KT - 1] = idx;
+#pragma unroll
+        for (int u = KT - 1; u > 0; --u) {
+            if (tv[u] > tv[u - 1]) {
+                const float fv = tv[u]; tv[u] = tv[u - 1]; tv[u - 1] = fv;
+                const int fi = ti[u]; ti[u] = ti[u - 1]; ti[u - 1] = fi;
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ void sts_f32(uint32_t addr, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory"); }
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// Vocabulary launch: the operands are SWAPPED by the host -- the 128-row UMMA-A operand is the activation tile (TMEM lane
+// = decoder row) and the MT = 256 row UMMA-B operand is the weight tile (TMEM column = vocabulary entry) -- so each
+// epilogue thread owns ONE decoder row and 64 of the tile's logits: + bias, running max / sum-exp (EX2 with pre-scaled
+// argument), top-KT (value desc, index asc).  The epilogue is the launch's bottleneck (instruction issue), hence 16
+// epilogue warps: warp 4 + 4 cp + q drains columns [64 cp, 64 cp + 64) of TMEM lane quarter q.  The two warps of one
+// 128-entry chunk (cp = 2 half, 2 half + 1) merge through shared memory; the even one writes the chunk's partials
+// (chunk index = 2 * vocab tile + half).
+// PAIR: the 2-CTA launch (gemm_tc2_vocab_kernel): tiles are walked per CTA pair, this CTA owns row tile 2 * (pair's row
+// tile) + rank, and the "accumulator drained" arrival goes to the LEADER CTA's barrier (tempty_remote = its
+// shared::cluster address).
+template <int MT, bool PAIR = false>
+__device__ __forceinline__ void tc_epilogue_vocab4(uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty, const float* __restrict__ bias,
+                                                  const TcVocabPart vp, int V, int rows, int total, int m_tiles, int n_tiles,
+                                                  int warp, int lane, float* cbuf, uint32_t tempty_remote = 0u) {
+    static_assert(MT == 256, "the vocabulary epilogue is written for 256-entry tiles");
+    constexpr int KT = 4;
+    static_assert(2 + 2 * KT <= TC_CAND_SLOTS, "the exchange of the partials uses the candidate slots");
+    constexpr float kLog2e = 1.4426950408889634f;
+    const int q = warp & 3, cp = (warp - 4) >> 2, half = cp >> 1, sub = cp & 1;
+    // this thread's column of the candidate buffer: slot k at cslot + k * TC_SLOT_STRIDE; the partner thread (same row,
+    // other 64 entries of the chunk) is 128 threads away
+    const uint32_t cslot = smem_u32(cbuf + (threadIdx.x - 128));
+    const uint32_t pslot = cslot + 128u * 4u;                       // sub == 0 only: where the sub == 1 partner writes
+    const int bar_id = 1 + q * 2 + half;                            // named barrier of the two partner warps (64 threads)
+    uint32_t as = 0, aphase = 0;
+    const int t0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, tstep = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    for (int t = t0; t < total; t += tstep) {
+        int ks, mt, nt;
+        tc_tile_of<true>(t, 1, m_tiles, n_tiles, ks, mt, nt);
+        if (PAIR) nt = 2 * nt + (int)(blockIdx.x & 1);
+        mbar_wait(&tfull[as], aphase);
+        tc_fence_after();
+        const int r = nt * TC_BN + q * 32 + lane;                   // decoder row of this thread
+        const int vbase = mt * MT + cp * 64;                        // first vocabulary entry of this warp's columns
+        const bool live = nt * TC_BN + q * 32 < rows;               // warp-uniform (and equal in both partner warps)
+        float tv[KT]; int ti[KT];
+#pragma unroll
+        for (int j = 0; j < KT; ++j) { tv[j] = -INFINITY; ti[j] = -1; }
+        float m = -INFINITY, s = 0.f;
+        if (live) {
+            const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + as * MT + cp * 64;
+            bool scan_all;
+            {
+                // ---- KT = 4: two passes, so that the data-dependent insertion runs over ~6 candidates per row
+                //      instead of being dragged through every entry by whichever lane of the warp inserts ----
+                // pass 1: log-sum-exp statistics and the maxima of the 8 groups of 8 entries
+                float gm[8];
+#pragma unroll
+                for (int ci = 0; ci < 2; ++ci) {
+                    const int v0 = vbase + 32 * ci;
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) gm[4 * ci + g] = -INFINITY;
+                    if (v0 < V) {
+                        uint32_t v[32];
+                        tmem_ld32(tcol + 32 * ci, v);
+                        float x[32];
+                        tc_vocab_bias(v, x, bias, v0, V);
+                        if (vp.logits != nullptr && r < rows) {
+                            float* lp = vp.logits + (size_t)r * vp.ldl + v0;
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) if (v0 + j < V) lp[j] = x[j];
+                        }
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            float gg = x[8 * g];
+#pragma unroll
+                            for (int j = 1; j < 8; ++j) gg = fmaxf(gg, x[8 * g + j]);
+                            gm[4 * ci + g] = gg;
+                        }
+                        const float bm = fmaxf(fmaxf(gm[4 * ci], gm[4 * ci + 1]), fmaxf(gm[4 * ci + 2], gm[4 * ci + 3]));
+                        if (bm > m) {
+                            s = (m == -INFINITY) ? 0.f : s * tc_ex2((m - bm) * kLog2e);
+                            m = bm;
+                        }
+                        const float nm = -m * kLog2e;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) s += tc_ex2(fmaf(x[j], kLog2e, nm));   // padding: ex2(-inf) = 0
+                    }
+                }
+                // T = 4th largest group maximum: four distinct entries are >= T, so every top-4 entry is >= T
+                float t0v = -INFINITY, t1v = -INFINITY, t2v = -INFINITY, t3v = -INFINITY;
+#pragma unroll
+                for (int g = 0; g < 8; ++g) {
+                    float cgm = gm[g], hi;
+                    hi = fmaxf(t0v, cgm); cgm = fminf(t0v, cgm); t0v = hi;
+                    hi = fmaxf(t1v, cgm); cgm = fminf(t1v, cgm); t1v = hi;
+                    hi = fmaxf(t2v, cgm); cgm = fminf(t2v, cgm); t2v = hi;
+                    t3v = fmaxf(t3v, cgm);
+                }
+                t3v = fmaxf(t3v, -3.0e38f);                         // fewer than 4 groups: every real entry, never the -inf padding
+                // pass 2: entries >= T go to this thread's column of the candidate buffer, their positions into one bit
+                // mask per 32 entries
+                uint32_t mk[2] = {0u, 0u};
+                uint32_t wp = cslot;                                 // write pointer, clamped to slot TC_CAND every 4 entries
+#pragma unroll
+                for (int ci = 0; ci < 2; ++ci) {
+                    const int v0 = vbase + 32 * ci;
+                    if (v0 < V) {
+                        uint32_t v[32];
+                        tmem_ld32(tcol + 32 * ci, v);
+                        float x[32];
+                        tc_vocab_bias(v, x, bias, v0, V);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            if (x[j] >= t3v) {
+                                sts_f32(wp, x[j]);
+                                wp += TC_SLOT_STRIDE;
+                                mk[ci] |= 1u << j;
+                            }
+                            if ((j & 3) == 3) wp = min(wp, cslot + TC_CAND * TC_SLOT_STRIDE);
+                        }
+                    }
+                }
+                const int ncand = __popc(mk[0]) + __popc(mk[1]);
+                // more than TC_CAND candidates in some lane (many equal logits; practically never): the whole warp walks
+                // everything -- warp-uniform, because the walk below re-reads TMEM with .sync.aligned loads
+                scan_all = __any_sync(0xffffffffu, ncand > TC_CAND);
+                if (!scan_all) {
+                    // pass 3: sorted insertion of the candidates in ascending index order
+                    uint32_t cur = mk[0];
+                    int ci = 0;
+                    for (int k = 0; k < ncand; ++k) {
+                        if (cur == 0u) { ci = 1; cur = mk[1]; }
+                        const int j = __ffs(cur) - 1;
+                        cur &= cur - 1u;
+                        tc_topk_insert<KT>(tv, ti, lds_f32(cslot + TC_SLOT_STRIDE * (uint32_t)k), vbase + 32 * ci + j);
+                    }
+                }
+            }
+            const bool stats = false;                               // m, s and the logits are done above
+#pragma unroll 1
+            for (int c0 = 0; c0 < (scan_all ? 64 : 0); c0 += 32) {
+                const int v0 = vbase + c0;
+                if (v0 >= V) break;                                 // entries past V: the chunk stays (or ends) empty
+                uint32_t v[32];
+                tmem_ld32(tcol + c0, v);
+                float x[32];
+                tc_vocab_bias(v, x, bias, v0, V);
+                float bm = x[0];
+#pragma unroll
+                for (int j = 1; j < 32; ++j) bm = fmaxf(bm, x[j]);
+                if (stats) {
+                    if (vp.logits != nullptr && r < rows) {
+                        float* lp = vp.logits + (size_t)r * vp.ldl + v0;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) if (v0 + j < V) lp[j] = x[j];
+                    }
+                    if (bm > m) {
+                        s = (m == -INFINITY) ? 0.f : s * tc_ex2((m - bm) * kLog2e);
+                        m = bm;
+                    }
+                    const float nm = -m * kLog2e;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) s += tc_ex2(fmaf(x[j], kLog2e, nm));   // padding: ex2(-inf) = 0
+                }
+                if (bm > tv[KT - 1]) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) tc_topk_insert<KT>(tv, ti, x[j], v0 + j);
+                }
+            }
+        }
+        // the accumulator is drained: hand it back before the (cheap) merge
+        tc_fence_before();
+        if (PAIR) mbar_arrive_cluster(tempty_remote + 8u * as);
+        else mbar_arrive(&tempty[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+
+        if (live) {
+            // ---- merge the two 64-entry halves of the chunk: the upper one hands {max, sum, top-KT} over in its own
+            //      candidate slots; all its indices are higher, so strict-> insertion keeps the lowest index first ----
+            if (sub == 1) {
+                sts_f32(cslot, m);
+                sts_f32(cslot + TC_SLOT_STRIDE, s);
+#pragma unroll
+                for (int j = 0; j < KT; ++j) {
+                    sts_f32(cslot + (2 + 2 * j) * TC_SLOT_STRIDE, tv[j]);
+                    sts_f32(cslot + (3 + 2 * j) * TC_SLOT_STRIDE, __int_as_float(ti[j]));
+                }
+            }
+            named_bar_sync(bar_id, 64);
+            if (sub == 0) {
+                const float m1 = lds_f32(pslot), s1 = lds_f32(pslot + TC_SLOT_STRIDE);
+#pragma unroll
+                for (int j = 0; j < KT; ++j)
+                    tc_topk_insert<KT>(tv, ti, lds_f32(pslot + (2 + 2 * j) * TC_SLOT_STRIDE),
+                                       __float_as_int(lds_f32(pslot + (3 + 2 * j) * TC_SLOT_STRIDE)));
+                const float mm = fmaxf(m, m1);
+                if (mm > -INFINITY) s = s * tc_ex2((m - mm) * kLog2e) + s1 * tc_ex2((m1 - mm) * kLog2e);   // ex2(-inf) = 0
+                m = mm;
+            }
+            named_bar_sync(bar_id, 64);                              // the slots may be overwritten by the next tile's candidates
+            if (sub == 0 && r < rows) {
+                const size_t ci = (size_t)r * vp.n_chunk + (size_t)(mt * 2 + half);
+                vp.chunk_max[ci] = m;
+                vp.chunk_sum[ci] = s;
+#pragma unroll
+                for (int j = 0; j < KT; j += 4) {
+                    *reinterpret_cast<float4*>(vp.cand_val + ci * KT + j) = make_float4(tv[j], tv[j + 1], tv[j + 2], tv[j + 3]);
+                    *reinterpret_cast<int4*>(vp.cand_idx + ci * KT + j) = make_int4(ti[j], ti[j + 1], ti[j + 2], ti[j + 3]);
+                }
+            }
+        }
+    }
+}
+
+// ---- beam widths 5..16 (KT = 8, 16): 8 epilogue warps, each thread walks its 128 logits with a sorted insertion ----
 // PAIR: the 2-CTA launch (gemm_tc2_vocab_kernel): tiles are walked per CTA pair, this CTA owns row tile 2 * (pair's row
 // tile) + rank, and the "accumulator drained" arrival goes to the LEADER CTA's barrier (tempty_remote = its
 // shared::cluster address).
 template <int MT, int KT, bool PAIR = false>
 __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty, const float* __restrict__ bias,
                                                   const TcVocabPart vp, int V, int rows, int total, int m_tiles, int n_tiles,
-                                                  int warp, int lane, float* cbuf, uint32_t tempty_remote = 0u) {
+                                                  int warp, int lane, uint32_t tempty_remote = 0u) {
     static_assert(MT == 256, "the vocabulary epilogue is written for 256-entry tiles");
     constexpr float kLog2e = 1.4426950408889634f;
     const int q = warp & 3, half = (warp - 4) >> 2;
-    float* const cslot = cbuf + (threadIdx.x - 128);                // candidate values of this thread: cslot[k * 256]
     uint32_t as = 0, aphase = 0;
     const int t0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, tstep = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
     for (int t = t0; t < total; t += tstep) {
@@ -215,102 +450,8 @@ __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* 
 #pragma unroll
             for (int j = 0; j < KT; ++j) { tv[j] = -INFINITY; ti[j] = -1; }
             float m = -INFINITY, s = 0.f;
-            bool scan_all = true;                                   // top-KT by walking every entry (the KT > 4 path)
-            if constexpr (KT == 4) {
-                // ---- KT = 4: two passes, so that the data-dependent insertion runs over ~6 candidates per row
-                //      instead of being dragged through all 128 entries by whichever lane of the warp inserts ----
-                const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + as * MT + half * 128;
-                // pass 1: log-sum-exp statistics and the maxima of the 8 groups of 16 entries
-                float gm[8];
-#pragma unroll
-                for (int ci = 0; ci < 4; ++ci) {
-                    const int v0 = vbase + 32 * ci;
-                    gm[2 * ci] = -INFINITY; gm[2 * ci + 1] = -INFINITY;
-                    if (v0 < V) {
-                        uint32_t v[32];
-                        tmem_ld32(tcol + 32 * ci, v);
-                        float x[32];
-                        tc_vocab_bias(v, x, bias, v0, V);
-                        if (vp.logits != nullptr && r < rows) {
-                            float* lp = vp.logits + (size_t)r * vp.ldl + v0;
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) if (v0 + j < V) lp[j] = x[j];
-                        }
-                        float g0 = x[0], g1 = x[16];
-#pragma unroll
-                        for (int j = 1; j < 16; ++j) { g0 = fmaxf(g0, x[j]); g1 = fmaxf(g1, x[16 + j]); }
-                        gm[2 * ci] = g0; gm[2 * ci + 1] = g1;
-                        const float bm = fmaxf(g0, g1);
-                        if (bm > m) {
-                            s = (m == -INFINITY) ? 0.f : s * tc_ex2((m - bm) * kLog2e);
-                            m = bm;
-                        }
-                        const float nm = -m * kLog2e;
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) s += tc_ex2(fmaf(x[j], kLog2e, nm));   // padding: ex2(-inf) = 0
-                    }
-                }
-                // T = 4th largest group maximum: four distinct entries are >= T, so every top-4 entry is >= T
-                float t0 = -INFINITY, t1 = -INFINITY, t2 = -INFINITY, t3 = -INFINITY;
-#pragma unroll
-                for (int g = 0; g < 8; ++g) {
-                    float cgm = gm[g], hi;
-                    hi = fmaxf(t0, cgm); cgm = fminf(t0, cgm); t0 = hi;
-                    hi = fmaxf(t1, cgm); cgm = fminf(t1, cgm); t1 = hi;
-                    hi = fmaxf(t2, cgm); cgm = fminf(t2, cgm); t2 = hi;
-                    t3 = fmaxf(t3, cgm);
-                }
-                // pass 2: entries >= T go to this thread's column of the candidate buffer (ring of TC_CAND slots), their
-                // positions into one bit mask per 32 entries
-                uint32_t mk[4] = {0u, 0u, 0u, 0u};
-                uint32_t wofs = 0u;
-#pragma unroll
-                for (int ci = 0; ci < 4; ++ci) {
-                    const int v0 = vbase + 32 * ci;
-                    if (v0 < V) {
-                        uint32_t v[32];
-                        tmem_ld32(tcol + 32 * ci, v);
-                        float x[32];
-                        tc_vocab_bias(v, x, bias, v0, V);
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            if (x[j] >= t3 && x[j] > -INFINITY) {
-                                cslot[wofs] = x[j];
-                                wofs = (wofs + 256u) & (TC_CAND * 256u - 1u);
-                                mk[ci] |= 1u << j;
-                            }
-                        }
-                    }
-                }
-                const int ncand = __popc(mk[0]) + __popc(mk[1]) + __popc(mk[2]) + __popc(mk[3]);
-                // ring overflowed in some lane (many equal logits; practically never): the whole warp walks everything --
-                // warp-uniform, because the walk below re-reads TMEM with .sync.aligned loads
-                scan_all = __any_sync(0xffffffffu, ncand > TC_CAND);
-                if (!scan_all) {
-                    // pass 3: sorted insertion of the candidates, ascending index (strict > keeps the lowest index first)
-                    uint32_t cur = mk[0];
-                    int ci = 0;
-                    for (int k = 0; k < ncand; ++k) {
-                        while (cur == 0u) { ++ci; cur = (ci == 1) ? mk[1] : (ci == 2) ? mk[2] : mk[3]; }
-                        const int j = __ffs(cur) - 1;
-                        cur &= cur - 1u;
-                        const float xv = cslot[k * 256];
-                        if (xv > tv[3]) {
-                            tv[3] = xv; ti[3] = vbase + 32 * ci + j;
-#pragma unroll
-                            for (int u = 3; u > 0; --u) {
-                                if (tv[u] > tv[u - 1]) {
-                                    const float fv = tv[u]; tv[u] = tv[u - 1]; tv[u - 1] = fv;
-                                    const int fi = ti[u]; ti[u] = ti[u - 1]; ti[u - 1] = fi;
-                                }
-                            }
-                        }
-                    }
-                }
-            }
-            const bool stats = (KT != 4);                           // the KT = 4 path already has m, s and the logits
 #pragma unroll 1
-            for (int c0 = 0; c0 < (scan_all ? 128 : 0); c0 += 32) {
+            for (int c0 = 0; c0 < 128; c0 += 32) {
                 const int v0 = vbase + c0;
                 if (v0 >= V) break;                                 // entries past V: the chunk stays (or ends) empty
                 uint32_t v[32];
@@ -337,20 +478,18 @@ __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* 
                         bm = fmaxf(bm, x[j]);
                     }
                 }
-                if (stats) {
-                    if (vp.logits != nullptr && r < rows) {
-                        float* lp = vp.logits + (size_t)r * vp.ldl + v0;
+                if (vp.logits != nullptr && r < rows) {
+                    float* lp = vp.logits + (size_t)r * vp.ldl + v0;
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) if (v0 + j < V) lp[j] = x[j];
-                    }
-                    if (bm > m) {
-                        s = (m == -INFINITY) ? 0.f : s * tc_ex2((m - bm) * kLog2e);
-                        m = bm;
-                    }
-                    const float nm = -m * kLog2e;
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) s += tc_ex2(fmaf(x[j], kLog2e, nm));   // padding: ex2(-inf) = 0
+                    for (int j = 0; j < 32; ++j) if (v0 + j < V) lp[j] = x[j];
                 }
+                if (bm > m) {
+                    s = (m == -INFINITY) ? 0.f : s * tc_ex2((m - bm) * kLog2e);
+                    m = bm;
+                }
+                const float nm = -m * kLog2e;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) s += tc_ex2(fmaf(x[j], kLog2e, nm));       // padding: ex2(-inf) = 0
                 if (bm > tv[KT - 1]) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
@@ -438,7 +577,7 @@ __device__ __forceinline__ void tc_epilogue(uint32_t tmem_base, uint64_t* tfull,
 }
 
 template <int MT, int EPI>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(EPI == ITB_EPI_VOCAB_K4 ? TC_VOC_THREADS : TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
                const ItbCtl* __restrict__ ctl, const float* __restrict__ bias, void* __restrict__ out, int M, int N,
                int K, int ldo, int act_f16, int nsplit, size_t part_stride, const TcVocabPart vp) {
@@ -456,7 +595,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
     uint64_t* tfull = bars + 2 * Cfg::kStages;
     uint64_t* tempty = tfull + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-    float* cbuf = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);   // vocabulary launches only (kVocabExtra)
+    float* cbuf = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);   // ITB_EPI_VOCAB_K4 launches only
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_tiles = (N + TC_BN - 1) / TC_BN, m_tiles = (M + MT - 1) / MT;
@@ -469,7 +608,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < Cfg::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 256); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], EPI == ITB_EPI_VOCAB_K4 ? 32 * TC_VOC_EPI_WARPS : 256); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -554,9 +693,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
             }
         }
     } else if (warp >= 4) {
-        if constexpr (EPI == ITB_EPI_VOCAB_K4) tc_epilogue_vocab<MT, 4>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane, cbuf);
-        else if constexpr (EPI == ITB_EPI_VOCAB_K8) tc_epilogue_vocab<MT, 8>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane, cbuf);
-        else if constexpr (EPI == ITB_EPI_VOCAB_K16) tc_epilogue_vocab<MT, 16>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane, cbuf);
+        if constexpr (EPI == ITB_EPI_VOCAB_K4) tc_epilogue_vocab4<MT>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane, cbuf);
+        else if constexpr (EPI == ITB_EPI_VOCAB_K8) tc_epilogue_vocab<MT, 8>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane);
+        else if constexpr (EPI == ITB_EPI_VOCAB_K16) tc_epilogue_vocab<MT, 16>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane);
         else if constexpr (EPI == ITB_EPI_BIAS_F32) tc_epilogue<MT, EPI, float>(tmem_base, tfull, tempty, bias, reinterpret_cast<float*>(out), M, N, ldo, nsplit, part_stride, total, m_tiles, warp, lane);
         else if (act_f16) tc_epilogue<MT, EPI, __half>(tmem_base, tfull, tempty, bias, reinterpret_cast<__half*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane);
         else tc_epilogue<MT, EPI, __nv_bfloat16>(tmem_base, tfull, tempty, bias, reinterpret_cast<__nv_bfloat16*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane);
@@ -578,10 +717,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
 // and issues the MMAs; "stage free" and "accumulator ready" are multicast to both CTAs by tcgen05.commit.
 #define TC2_HALF_BYTES (128 * TC_BK * 2)          // one 128-row operand tile of a stage (16 KB)
 #define TC2_STAGES 6
-#define TC2_SMEM (TC2_STAGES * 2 * TC2_HALF_BYTES + 1024 + 256 + TC_CAND * 256 * 4)
+#define TC2_SMEM (TC2_STAGES * 2 * TC2_HALF_BYTES + 1024 + 256 + TC_CAND_SLOTS * 32 * TC_VOC_EPI_WARPS * 4)
 
 template <int KT>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(KT == 4 ? TC_VOC_THREADS : TC_THREADS, 1)
 gemm_tc2_vocab_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmWv,
                       const ItbCtl* __restrict__ ctl, const float* __restrict__ bias, int V, int rows, int K, int act_f16,
                       const TcVocabPart vp) {
@@ -610,7 +749,7 @@ gemm_tc2_vocab_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_cons
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < TC2_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 512); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], KT == 4 ? 2 * 32 * TC_VOC_EPI_WARPS : 512); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -690,7 +829,8 @@ gemm_tc2_vocab_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_cons
             }
         }
     } else if (warp >= 4) {
-        tc_epilogue_vocab<256, KT, true>(tmem_base, tfull, tempty, bias, vp, V, rows, total, v_tiles, rp_tiles, warp, lane, cbuf, tempty_l);
+        if constexpr (KT == 4) tc_epilogue_vocab4<256, true>(tmem_base, tfull, tempty, bias, vp, V, rows, total, v_tiles, rp_tiles, warp, lane, cbuf, tempty_l);
+        else tc_epilogue_vocab<256, KT, true>(tmem_base, tfull, tempty, bias, vp, V, rows, total, v_tiles, rp_tiles, warp, lane, tempty_l);
     }
 
     tc_fence_before();
@@ -777,7 +917,8 @@ void itb_tc_plan(int M, int N, int K, int max_split, int* mt_out, int* split_out
 template <int MT, int EPI>
 static int launch_tc(const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCtl* ctl, const float* bias, void* out,
                      int M, int N, int K, int ldo, int act_f16, int nsplit, cudaStream_t s, const TcVocabPart vp = TcVocabPart()) {
-    constexpr int kSmem = TcCfg<MT>::kSmemBytes + (EPI >= ITB_EPI_VOCAB_K4 ? TC_CAND * 256 * 4 : 0);   // + candidate buffer
+    constexpr int kSmem = TcCfg<MT>::kSmemBytes + (EPI == ITB_EPI_VOCAB_K4 ? TC_CAND_SLOTS * 32 * TC_VOC_EPI_WARPS * 4 : 0);   // + candidate buffer
+    constexpr int kThreads = EPI == ITB_EPI_VOCAB_K4 ? TC_VOC_THREADS : TC_THREADS;
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
@@ -786,7 +927,7 @@ static int launch_tc(const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCt
     }
     const int total = ((N + TC_BN - 1) / TC_BN) * ((M + MT - 1) / MT) * nsplit;
     const int grid = total < num_sms() ? total : num_sms();
-    cudaError_t e = itb_launch(gemm_tc_kernel<MT, EPI>, dim3(grid), dim3(TC_THREADS), (size_t)kSmem, s, tmW, tmA,
+    cudaError_t e = itb_launch(gemm_tc_kernel<MT, EPI>, dim3(grid), dim3(kThreads), (size_t)kSmem, s, tmW, tmA,
                                ctl, bias, out, M, N, K, ldo, act_f16, nsplit, (size_t)M * (size_t)ldo, vp);
     if (e != cudaSuccess) { itb_set_error("gemm_tc: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("gemm_tc");
@@ -832,7 +973,7 @@ static int launch_tc2_vocab(const CUtensorMap& tmX, const CUtensorMap& tmWv128, 
     const int total = ((rows + 255) / 256) * ((V + 255) / 256);
     const int cap = num_sms() & ~1;
     const int grid = 2 * total < cap ? 2 * total : cap;
-    cudaError_t e = itb_launch(gemm_tc2_vocab_kernel<KT>, dim3(grid), dim3(TC_THREADS), (size_t)TC2_SMEM, s, tmX, tmWv128, ctl, bias, V,
+    cudaError_t e = itb_launch(gemm_tc2_vocab_kernel<KT>, dim3(grid), dim3(KT == 4 ? TC_VOC_THREADS : TC_THREADS), (size_t)TC2_SMEM, s, tmX, tmWv128, ctl, bias, V,
                                rows, K, act_f16, vp);
     if (e != cudaSuccess) { itb_set_error("gemm_tc2: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("gemm_tc2");
