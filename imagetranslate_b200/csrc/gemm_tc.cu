@@ -129,6 +129,20 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// registers -> TMEM, same 32 lanes x 32 columns shape as tmem_ld32 (the epilogue parks its biased logits in the accumulator)
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const float* x) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "f"(x[0]), "f"(x[1]), "f"(x[2]), "f"(x[3]), "f"(x[4]), "f"(x[5]), "f"(x[6]), "f"(x[7]),
+          "f"(x[8]), "f"(x[9]), "f"(x[10]), "f"(x[11]), "f"(x[12]), "f"(x[13]), "f"(x[14]), "f"(x[15]),
+          "f"(x[16]), "f"(x[17]), "f"(x[18]), "f"(x[19]), "f"(x[20]), "f"(x[21]), "f"(x[22]), "f"(x[23]),
+          "f"(x[24]), "f"(x[25]), "f"(x[26]), "f"(x[27]), "f"(x[28]), "f"(x[29]), "f"(x[30]), "f"(x[31])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 template <int MT> struct TcCfg {
     static constexpr int kStageBytes = TC_BN * TC_BK * 2 + MT * TC_BK * 2;
     // small-MT tiles (latency-bound decode GEMMs) keep ~100 KB in flight so that two CTAs (the tail of one GEMM and
@@ -276,6 +290,7 @@ __device__ __forceinline__ void tc_epilogue_vocab4(uint32_t tmem_base, uint64_t*
                         tmem_ld32(tcol + 32 * ci, v);
                         float x[32];
                         tc_vocab_bias(v, x, bias, v0, V);
+                        tmem_st32(tcol + 32 * ci, x);                // park the biased logits for pass 2 (and the full walk)
                         if (vp.logits != nullptr && r < rows) {
                             float* lp = vp.logits + (size_t)r * vp.ldl + v0;
 #pragma unroll
@@ -313,18 +328,18 @@ __device__ __forceinline__ void tc_epilogue_vocab4(uint32_t tmem_base, uint64_t*
                 // mask per 32 entries
                 uint32_t mk[2] = {0u, 0u};
                 uint32_t wp = cslot;                                 // write pointer, clamped to slot TC_CAND every 4 entries
+                tmem_st_wait();
 #pragma unroll
                 for (int ci = 0; ci < 2; ++ci) {
                     const int v0 = vbase + 32 * ci;
                     if (v0 < V) {
                         uint32_t v[32];
-                        tmem_ld32(tcol + 32 * ci, v);
-                        float x[32];
-                        tc_vocab_bias(v, x, bias, v0, V);
+                        tmem_ld32(tcol + 32 * ci, v);                // biased logits (-inf past V), parked by pass 1
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
-                            if (x[j] >= t3v) {
-                                sts_f32(wp, x[j]);
+                            const float xj = __uint_as_float(v[j]);
+                            if (xj >= t3v) {
+                                sts_f32(wp, xj);
                                 wp += TC_SLOT_STRIDE;
                                 mk[ci] |= 1u << j;
                             }
@@ -348,36 +363,15 @@ __device__ __forceinline__ void tc_epilogue_vocab4(uint32_t tmem_base, uint64_t*
                     }
                 }
             }
-            const bool stats = false;                               // m, s and the logits are done above
+            // the full walk (m, s and the logits are done above; the accumulator holds the biased logits)
 #pragma unroll 1
             for (int c0 = 0; c0 < (scan_all ? 64 : 0); c0 += 32) {
                 const int v0 = vbase + c0;
                 if (v0 >= V) break;                                 // entries past V: the chunk stays (or ends) empty
                 uint32_t v[32];
                 tmem_ld32(tcol + c0, v);
-                float x[32];
-                tc_vocab_bias(v, x, bias, v0, V);
-                float bm = x[0];
 #pragma unroll
-                for (int j = 1; j < 32; ++j) bm = fmaxf(bm, x[j]);
-                if (stats) {
-                    if (vp.logits != nullptr && r < rows) {
-                        float* lp = vp.logits + (size_t)r * vp.ldl + v0;
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) if (v0 + j < V) lp[j] = x[j];
-                    }
-                    if (bm > m) {
-                        s = (m == -INFINITY) ? 0.f : s * tc_ex2((m - bm) * kLog2e);
-                        m = bm;
-                    }
-                    const float nm = -m * kLog2e;
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) s += tc_ex2(fmaf(x[j], kLog2e, nm));   // padding: ex2(-inf) = 0
-                }
-                if (bm > tv[KT - 1]) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) tc_topk_insert<KT>(tv, ti, x[j], v0 + j);
-                }
+                for (int j = 0; j < 32; ++j) tc_topk_insert<KT>(tv, ti, __uint_as_float(v[j]), v0 + j);
             }
         }
         // the accumulator is drained: hand it back before the (cheap) merge
