@@ -25,15 +25,13 @@
 #define DH 64
 #define AM_WARPS 4
 #define AM_THREADS (AM_WARPS * 32)
-#ifndef AM_STAGE
-#define AM_STAGE 64            // virtual positions staged in shared memory per round trip
-#endif
-#ifndef AM_MINB
-#define AM_MINB 3
-#endif
 #define AM_ROWB 272            // bytes per staged row: K 128 + V 128 + 16 pad
-#define AM_NCH (AM_STAGE / 32)  // 32-position chunks per stage
-#define AM_SMEM (AM_WARPS * AM_STAGE * AM_ROWB)
+// STAGE = virtual positions staged in shared memory per round trip (template parameter of the kernel).  Two builds:
+// STAGE 64 / 3 CTAs per SM (fewest round trips; launches of a wave or two, where latency is everything) and
+// STAGE 32 / 4 CTAs per SM (a third more warps in flight; many-wave launches, where the SM's issue rate is the limit).
+#define AM_NCH (STAGE / 32)     // 32-position chunks per stage
+#define AM_SMEM(STAGE) (AM_WARPS * (STAGE) * AM_ROWB)
+#define AM_MINB(STAGE) ((STAGE) == 64 ? 3 : 4)
 
 struct AttnMmaArgs {
     const ItbCtl* ctl;
@@ -82,8 +80,8 @@ __device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t&
     lo = Mma16<T>::pack(x - h.x, y - h.y);
 }
 
-template <typename T, bool SELF>
-__global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaArgs a) {
+template <typename T, bool SELF, int STAGE>
+__global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(AttnMmaArgs a) {
     pdl_trigger();
     const int lane = threadIdx.x & 31, nl = lane >> 2, c = lane & 3;       // nl: B-fragment column / C row; c: quad lane
     const int wg = blockIdx.x * AM_WARPS + (threadIdx.x >> 5);
@@ -92,12 +90,12 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
     const int h = wg % H, z = (wg / H) % nz, b = wg / (H * nz);
     const int q0 = z * 4, row0 = b * a.beam + q0, nq = min(4, a.beam - q0);
     const int hoff = h * DH;
-    // Per-warp staging buffer: AM_STAGE virtual rows of [K 128 B | V 128 B], padded to 272 B so that the fragment reads
+    // Per-warp staging buffer: STAGE virtual rows of [K 128 B | V 128 B], padded to 272 B so that the fragment reads
     // below are bank-conflict free.  All rows of a stage are requested with cp.async (16 B each, zero-filled when the
     // virtual position does not exist) BEFORE anything is consumed: one memory round trip per 64 positions, no
     // registers tied up by loads in flight.
     extern __shared__ __align__(16) unsigned char am_smem[];
-    unsigned char* ws = am_smem + (size_t)(threadIdx.x >> 5) * (AM_STAGE * AM_ROWB);
+    unsigned char* ws = am_smem + (size_t)(threadIdx.x >> 5) * (STAGE * AM_ROWB);
     const uint32_t ws_u32 = (uint32_t)__cvta_generic_to_shared(ws);
     const int part = lane & 15;                                     // 16-byte piece of the 256-byte row this lane copies
     const size_t part_off = (part < 8) ? (size_t)part * 8 : (size_t)d + (size_t)(part - 8) * 8;
@@ -111,7 +109,7 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
         const T* cbase = reinterpret_cast<const T*>(a.kv) + ((size_t)b * a.S * a.L + a.layer) * 2 * d + hoff;
         const size_t cstride = (size_t)a.L * 2 * d;
 #pragma unroll
-        for (int k = 0; k < AM_STAGE / 2; ++k) {
+        for (int k = 0; k < STAGE / 2; ++k) {
             const int row = 2 * k + (lane >> 4);
             if ((row & ~31) < a.S) {
                 const bool ok = row < a.S;
@@ -235,12 +233,19 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
     float m_run = -INFINITY, l_run = 0.f;
     const int qrow = nl & 3;             // rows 4..7 mirror rows 0..3 (their results are discarded)
 
-    for (int sb = 0; sb < nv; sb += AM_STAGE) {
+    // copy loop constants: a row offset travels as ONE 32-bit count of 16-byte units (row index x stride16), so a copy
+    // costs a shuffle, one wide multiply-add and the cp.async
+    constexpr uint32_t kNoRow = 0xFFFFFFFFu;
+    const uint32_t stride16 = (uint32_t)(pos_stride * sizeof(T) / 16);
+    const unsigned char* lane_src = reinterpret_cast<const unsigned char*>(base + part_off);
+    const uint32_t lane_dst = ws_u32 + (lane >> 4) * AM_ROWB + part * 16;
+    for (int sb = 0; sb < nv; sb += STAGE) {
         // ---- virtual positions sb + 32*hv + lane: row index and meta = owner mask (bits 0-3) | masked-source (bit 4) ----
-        int rowidx[AM_NCH], meta[AM_NCH];
+        uint32_t rowidx[AM_NCH];                                     // row offset in 16-byte units, kNoRow = absent
+        int meta[AM_NCH];
 #pragma unroll
         for (int hv = 0; hv < AM_NCH; ++hv) {
-            rowidx[hv] = -1; meta[hv] = 0;
+            rowidx[hv] = kNoRow; meta[hv] = 0;
             const int v = sb + 32 * hv + lane;
             if (SELF) {
                 const bool in = v < nv, tail = in && v >= cshared;
@@ -253,10 +258,10 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
                 int slot = (qi == 0) ? s0 : (qi == 1) ? s1 : (qi == 2) ? s2 : s3;
                 if (in && p >= 32) slot = anc0[(size_t)qi * a.T_max + p];
                 if (tail && p == n - 1) slot = q0 + qi;                          // the row appended above
-                if (in) { rowidx[hv] = (b * a.beam + slot) * a.T_max + p; meta[hv] = tail ? (1 << qi) : 0xF; }
+                if (in) { rowidx[hv] = (uint32_t)((b * a.beam + slot) * a.T_max + p) * stride16; meta[hv] = tail ? (1 << qi) : 0xF; }
             } else if (v < nv) {
                 {
-                    rowidx[hv] = v;
+                    rowidx[hv] = (uint32_t)v * stride16;
                     const int mk = (sb == 0) ? mk0[hv] : ((mrow != nullptr) ? (int)mrow[v] : 1);
                     meta[hv] = 0xF | ((mk == 0) ? 0x10 : 0);
                 }
@@ -264,14 +269,13 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
         }
         const int nchunk = min(AM_NCH, (nv - sb + 31) >> 5);         // 32-position chunks in this stage (warp-uniform)
 #pragma unroll
-        for (int k = 0; k < AM_STAGE / 2; ++k) {
+        for (int k = 0; k < STAGE / 2; ++k) {
             if (k < 16 * nchunk && (SELF || sb != 0)) {              // cross: stage 0 was requested at the top
-                const int row = 2 * k + (lane >> 4);
-                const int r = __shfl_sync(0xffffffffu, rowidx[k >> 4], row & 31);
-                const T* src = base + ((r >= 0) ? (size_t)r * pos_stride + part_off : (size_t)0);
-                const uint32_t dst = ws_u32 + row * AM_ROWB + part * 16;
-                const int nbytes = (r >= 0) ? 16 : 0;
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nbytes) : "memory");
+                const uint32_t o = __shfl_sync(0xffffffffu, rowidx[k >> 4], (2 * k + (lane >> 4)) & 31);
+                const bool ok = o != kNoRow;
+                const unsigned char* src = lane_src + (size_t)(ok ? o : 0u) * 16;
+                const int nbytes = ok ? 16 : 0;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(lane_dst + 2 * k * AM_ROWB), "l"(src), "r"(nbytes) : "memory");
             }
         }
         asm volatile("cp.async.wait_all;" ::: "memory");
@@ -365,22 +369,35 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB) attn_mma_kernel(AttnMmaAr
     }
 }
 
+template <typename T, int STAGE>
+static int launch_attn_mma_stage(const AttnMmaArgs& a, bool self, cudaStream_t s) {
+    const dim3 grid((a.n_warps + AM_WARPS - 1) / AM_WARPS), block(AM_THREADS);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e1 = cudaFuncSetAttribute(attn_mma_kernel<T, true, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, AM_SMEM(STAGE));
+        cudaError_t e2 = cudaFuncSetAttribute(attn_mma_kernel<T, false, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, AM_SMEM(STAGE));
+        if (e1 != cudaSuccess || e2 != cudaSuccess) { itb_set_error("attention: cudaFuncSetAttribute failed"); return -1; }
+        attr_set = true;
+    }
+    cudaError_t e = self ? itb_launch(attn_mma_kernel<T, true, STAGE>, grid, block, (size_t)AM_SMEM(STAGE), s, a)
+                         : itb_launch(attn_mma_kernel<T, false, STAGE>, grid, block, (size_t)AM_SMEM(STAGE), s, a);
+    if (e != cudaSuccess) { itb_set_error("%s: launch failed: %s", self ? "self_attention" : "cross_attention", cudaGetErrorString(e)); return -1; }
+    return itb_check_launch(self ? "self_attention" : "cross_attention");
+}
+
 template <typename T>
 static int launch_attn_mma(AttnMmaArgs a, bool self, cudaStream_t s) {
     const int B = a.M / a.beam, H = a.d / DH;
     a.n_warps = B * H * ((a.beam + 3) / 4);
-    const dim3 grid((a.n_warps + AM_WARPS - 1) / AM_WARPS), block(AM_THREADS);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e1 = cudaFuncSetAttribute(attn_mma_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AM_SMEM);
-        cudaError_t e2 = cudaFuncSetAttribute(attn_mma_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AM_SMEM);
-        if (e1 != cudaSuccess || e2 != cudaSuccess) { itb_set_error("attention: cudaFuncSetAttribute failed"); return -1; }
-        attr_set = true;
+    // more than ~2 waves of the 3-CTA build (148 SMs x 12 warps): occupancy beats round trips (measured at 4096 rows:
+    // step -28 us; at 244 rows the 64-position build is 25 us per step faster)
+    static int forced = -1;
+    if (forced < 0) {
+        const char* e = getenv("ITB_ATTN_STAGE");
+        forced = (e != nullptr) ? atoi(e) : 0;
     }
-    cudaError_t e = self ? itb_launch(attn_mma_kernel<T, true>, grid, block, (size_t)AM_SMEM, s, a)
-                         : itb_launch(attn_mma_kernel<T, false>, grid, block, (size_t)AM_SMEM, s, a);
-    if (e != cudaSuccess) { itb_set_error("%s: launch failed: %s", self ? "self_attention" : "cross_attention", cudaGetErrorString(e)); return -1; }
-    return itb_check_launch(self ? "self_attention" : "cross_attention");
+    const bool small_stage = forced != 0 ? forced == 32 : a.n_warps > 2 * 148 * 12;
+    return small_stage ? launch_attn_mma_stage<T, 32>(a, self, s) : launch_attn_mma_stage<T, 64>(a, self, s);
 }
 
 // Called by itb_self_attention / itb_cross_attention (attention.cu) for the 16-bit dtypes.
