@@ -232,7 +232,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
         } else {
             // log-sum-exp over the chunk partials, then a streaming top-K over the n_chunk * KT chunk candidates with the
             // warp-level sorted list (entry j in lane j) and its threshold -- any number of chunks, no staging buffer
-            const int nc = a.n_chunk, n = nc * KT;
+            const int nc = a.n_chunk;
             const float* cmp = a.chunk_max + (size_t)rr * nc;
             const float* csp = a.chunk_sum + (size_t)rr * nc;
             float mm = -INFINITY;
@@ -245,18 +245,53 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
             }
             ss = warp_sum(ss);
             const float logz = logf(ss);
+            // T = K-th largest chunk maximum (a real logit each): a lower bound of the row's K-th largest logit, so only
+            // chunks whose maximum reaches T can hold a top-K entry -- typically K..2K of the n_chunk chunks.  Found with
+            // the warp-level sorted list (entry j in lane j) over the maxima alone.
+            float tl = -INFINITY, T = -INFINITY;
+            for (int ci0 = 0; ci0 < nc; ci0 += 32) {
+                const int ci = ci0 + lane;
+                const float cm = ci < nc ? __ldcg(cmp + ci) : -INFINITY;
+                unsigned q = __ballot_sync(0xffffffffu, cm > T);
+                while (q != 0u) {
+                    const int src = __ffs(q) - 1;
+                    q &= q - 1;
+                    const float cx = __shfl_sync(0xffffffffu, cm, src);
+                    if (cx > T) {                                            // warp-uniform; T may have risen meanwhile
+                        const int pos = __popc(__ballot_sync(0xffffffffu, lane < K && tl >= cx));
+                        const float uv = __shfl_up_sync(0xffffffffu, tl, 1);
+                        if (lane < K) {
+                            if (lane == pos) tl = cx;
+                            else if (lane > pos) tl = uv;
+                        }
+                        T = __shfl_sync(0xffffffffu, tl, K - 1);
+                    }
+                }
+            }
+            // streaming top-K over the candidates of the qualifying chunks: in every batch of 32 chunks the lane of a
+            // qualifying chunk loads that chunk's KT (value, index) pairs (one round trip for the batch), then the warp
+            // inserts rank by rank with the list's threshold -- any number of chunks, no staging buffer
             float lv = -INFINITY; int li = INT_MAX;
             float thr = -INFINITY;
-            for (int i0 = 0; i0 < n; i0 += 32 * 8) {                    // 8 candidates per lane requested at once
-                float xv[8]; int xj[8];
+            for (int ci0 = 0; ci0 < nc; ci0 += 32) {
+                const int ci = ci0 + lane;
+                const float cm = ci < nc ? __ldcg(cmp + ci) : -INFINITY;
+                const bool mine = cm >= T && cm > -INFINITY;
+                if (__ballot_sync(0xffffffffu, mine) == 0u) continue;
+                float xv[KT]; int xj[KT];
 #pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const int i = i0 + u * 32 + lane;
-                    xv[u] = -INFINITY; xj[u] = -1;
-                    if (i < n) { xv[u] = __ldcg(a.cand_val + (size_t)rr * n + i); xj[u] = __ldcg(a.cand_idx + (size_t)rr * n + i); }
+                for (int u = 0; u < KT; u += 4) {
+                    float4 v4 = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+                    int4 j4 = make_int4(-1, -1, -1, -1);
+                    if (mine) {
+                        v4 = __ldcg(reinterpret_cast<const float4*>(a.cand_val + ((size_t)rr * nc + ci) * KT + u));
+                        j4 = __ldcg(reinterpret_cast<const int4*>(a.cand_idx + ((size_t)rr * nc + ci) * KT + u));
+                    }
+                    xv[u] = v4.x; xv[u + 1] = v4.y; xv[u + 2] = v4.z; xv[u + 3] = v4.w;
+                    xj[u] = j4.x; xj[u + 1] = j4.y; xj[u + 2] = j4.z; xj[u + 3] = j4.w;
                 }
 #pragma unroll
-                for (int u = 0; u < 8; ++u) {
+                for (int u = 0; u < KT; ++u) {
                     unsigned q = __ballot_sync(0xffffffffu, xj[u] >= 0 && xv[u] >= thr && xv[u] > -INFINITY);
                     while (q != 0u) {
                         const int src = __ffs(q) - 1;
