@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     __shared__ float s_rtop_val[8][16];
     __shared__ int s_rtop_idx[8][16];
     __shared__ int s_src[16], s_word[16];
+    __shared__ int s_q[8][64];            // phase 2: per-warp queue of qualifying chunk indices
     __shared__ int s_last;
 
     pdl_trigger();
@@ -235,49 +236,14 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
             const int nc = a.n_chunk;
             const float* cmp = a.chunk_max + (size_t)rr * nc;
             const float* csp = a.chunk_sum + (size_t)rr * nc;
-            float mm = -INFINITY;
-            for (int ci = lane; ci < nc; ci += 32) mm = fmaxf(mm, __ldcg(cmp + ci));
-            mm = warp_max(mm);
-            float ss = 0.f;
-            for (int ci = lane; ci < nc; ci += 32) {
-                const float cm = __ldcg(cmp + ci);
-                if (cm != -INFINITY) ss += __ldcg(csp + ci) * expf(cm - mm);
-            }
-            ss = warp_sum(ss);
-            const float logz = logf(ss);
-            // T = K-th largest chunk maximum (a real logit each): a lower bound of the row's K-th largest logit, so only
-            // chunks whose maximum reaches T can hold a top-K entry -- typically K..2K of the n_chunk chunks.  Found with
-            // the warp-level sorted list (entry j in lane j) over the maxima alone.
-            float tl = -INFINITY, T = -INFINITY;
-            for (int ci0 = 0; ci0 < nc; ci0 += 32) {
-                const int ci = ci0 + lane;
-                const float cm = ci < nc ? __ldcg(cmp + ci) : -INFINITY;
-                unsigned q = __ballot_sync(0xffffffffu, cm > T);
-                while (q != 0u) {
-                    const int src = __ffs(q) - 1;
-                    q &= q - 1;
-                    const float cx = __shfl_sync(0xffffffffu, cm, src);
-                    if (cx > T) {                                            // warp-uniform; T may have risen meanwhile
-                        const int pos = __popc(__ballot_sync(0xffffffffu, lane < K && tl >= cx));
-                        const float uv = __shfl_up_sync(0xffffffffu, tl, 1);
-                        if (lane < K) {
-                            if (lane == pos) tl = cx;
-                            else if (lane > pos) tl = uv;
-                        }
-                        T = __shfl_sync(0xffffffffu, tl, K - 1);
-                    }
-                }
-            }
-            // streaming top-K over the candidates of the qualifying chunks: in every batch of 32 chunks the lane of a
-            // qualifying chunk loads that chunk's KT (value, index) pairs (one round trip for the batch), then the warp
-            // inserts rank by rank with the list's threshold -- any number of chunks, no staging buffer
-            float lv = -INFINITY; int li = INT_MAX;
+            float mm = -INFINITY, ss = 0.f, logz = 0.f;
+            float lv = -INFINITY; int li = INT_MAX;                  // the row's sorted top-KT list: entry j in lane j
             float thr = -INFINITY;
-            for (int ci0 = 0; ci0 < nc; ci0 += 32) {
-                const int ci = ci0 + lane;
-                const float cm = ci < nc ? __ldcg(cmp + ci) : -INFINITY;
-                const bool mine = cm >= T && cm > -INFINITY;
-                if (__ballot_sync(0xffffffffu, mine) == 0u) continue;
+            // inserts the KT candidates of up to 32 chunks (lane l < k owns chunk s_q[w][l]): one round trip for all of
+            // them, then rank by rank with the list's threshold
+            auto insert_chunks = [&](int k) {
+                const bool mine = lane < k;
+                const int ci = mine ? s_q[w][lane] : 0;
                 float xv[KT]; int xj[KT];
 #pragma unroll
                 for (int u = 0; u < KT; u += 4) {
@@ -307,6 +273,144 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
                             else if (lane > pos) { lv = uv; li = ui; }
                         }
                         thr = __shfl_sync(0xffffffffu, lv, KT - 1);
+                    }
+                }
+            };
+            constexpr int CPL = 16;                                  // chunks per lane held in registers
+            if (nc <= 32 * CPL) {
+                // ---- the usual case (V <= 65536): every chunk maximum / sum of the row is loaded ONCE, all loads in
+                //      flight together; the passes below (max, sum, threshold, queue) run from registers -- the looped
+                //      form paid a dependent memory round trip per 32 chunks and pass, which was the whole kernel ----
+                float cmr[CPL], csr[CPL];
+#pragma unroll
+                for (int j = 0; j < CPL; ++j) {
+                    const int ci = j * 32 + lane;
+                    cmr[j] = ci < nc ? __ldcg(cmp + ci) : -INFINITY;
+                    csr[j] = ci < nc ? __ldcg(csp + ci) : 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < CPL; ++j) mm = fmaxf(mm, cmr[j]);
+                mm = warp_max(mm);
+#pragma unroll
+                for (int j = 0; j < CPL; ++j)
+                    if (cmr[j] != -INFINITY) ss += csr[j] * expf(cmr[j] - mm);        // same order as the looped form
+                ss = warp_sum(ss);
+                logz = logf(ss);
+                // T = K-th largest chunk maximum (a real logit each): a lower bound of the row's K-th largest logit, so
+                // only chunks whose maximum reaches T can hold a top-K entry -- typically K..2K of them
+                float tl = -INFINITY, T = -INFINITY;
+#pragma unroll
+                for (int j = 0; j < CPL; ++j) {
+                    unsigned q = __ballot_sync(0xffffffffu, cmr[j] > T);
+                    while (q != 0u) {
+                        const int src = __ffs(q) - 1;
+                        q &= q - 1;
+                        const float cx = __shfl_sync(0xffffffffu, cmr[j], src);
+                        if (cx > T) {                                        // warp-uniform; T may have risen meanwhile
+                            const int pos = __popc(__ballot_sync(0xffffffffu, lane < K && tl >= cx));
+                            const float uv = __shfl_up_sync(0xffffffffu, tl, 1);
+                            if (lane < K) {
+                                if (lane == pos) tl = cx;
+                                else if (lane > pos) tl = uv;
+                            }
+                            T = __shfl_sync(0xffffffffu, tl, K - 1);
+                        }
+                    }
+                }
+                // queue the qualifying chunks (compacted over the warp), insert them 32 at a time
+                int cnt = 0;
+#pragma unroll
+                for (int j = 0; j < CPL; ++j) {
+                    const bool mine = cmr[j] >= T && cmr[j] > -INFINITY;
+                    const unsigned bal = __ballot_sync(0xffffffffu, mine);
+                    if (bal != 0u) {
+                        if (mine) s_q[w][cnt + __popc(bal & ((1u << lane) - 1u))] = j * 32 + lane;
+                        cnt += __popc(bal);
+                        if (cnt >= 32) {
+                            __syncwarp();
+                            insert_chunks(32);
+                            const int rem = cnt - 32;
+                            const int mv = lane < rem ? s_q[w][32 + lane] : 0;
+                            __syncwarp();
+                            if (lane < rem) s_q[w][lane] = mv;
+                            cnt = rem;
+                        }
+                    }
+                }
+                __syncwarp();
+                if (cnt > 0) insert_chunks(cnt);
+            } else {
+                mm = -INFINITY;
+                for (int ci = lane; ci < nc; ci += 32) mm = fmaxf(mm, __ldcg(cmp + ci));
+                mm = warp_max(mm);
+                ss = 0.f;
+                for (int ci = lane; ci < nc; ci += 32) {
+                    const float cm = __ldcg(cmp + ci);
+                    if (cm != -INFINITY) ss += __ldcg(csp + ci) * expf(cm - mm);
+                }
+                ss = warp_sum(ss);
+                logz = logf(ss);
+                // T = K-th largest chunk maximum (a real logit each): a lower bound of the row's K-th largest logit, so only
+                // chunks whose maximum reaches T can hold a top-K entry -- typically K..2K of the n_chunk chunks.  Found with
+                // the warp-level sorted list (entry j in lane j) over the maxima alone.
+                float tl = -INFINITY, T = -INFINITY;
+                for (int ci0 = 0; ci0 < nc; ci0 += 32) {
+                    const int ci = ci0 + lane;
+                    const float cm = ci < nc ? __ldcg(cmp + ci) : -INFINITY;
+                    unsigned q = __ballot_sync(0xffffffffu, cm > T);
+                    while (q != 0u) {
+                        const int src = __ffs(q) - 1;
+                        q &= q - 1;
+                        const float cx = __shfl_sync(0xffffffffu, cm, src);
+                        if (cx > T) {                                            // warp-uniform; T may have risen meanwhile
+                            const int pos = __popc(__ballot_sync(0xffffffffu, lane < K && tl >= cx));
+                            const float uv = __shfl_up_sync(0xffffffffu, tl, 1);
+                            if (lane < K) {
+                                if (lane == pos) tl = cx;
+                                else if (lane > pos) tl = uv;
+                            }
+                            T = __shfl_sync(0xffffffffu, tl, K - 1);
+                        }
+                    }
+                }
+                // streaming top-K over the candidates of the qualifying chunks: in every batch of 32 chunks the lane of a
+                // qualifying chunk loads that chunk's KT (value, index) pairs (one round trip for the batch), then the warp
+                // inserts rank by rank with the list's threshold -- any number of chunks, no staging buffer
+                for (int ci0 = 0; ci0 < nc; ci0 += 32) {
+                    const int ci = ci0 + lane;
+                    const float cm = ci < nc ? __ldcg(cmp + ci) : -INFINITY;
+                    const bool mine = cm >= T && cm > -INFINITY;
+                    if (__ballot_sync(0xffffffffu, mine) == 0u) continue;
+                    float xv[KT]; int xj[KT];
+    #pragma unroll
+                    for (int u = 0; u < KT; u += 4) {
+                        float4 v4 = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+                        int4 j4 = make_int4(-1, -1, -1, -1);
+                        if (mine) {
+                            v4 = __ldcg(reinterpret_cast<const float4*>(a.cand_val + ((size_t)rr * nc + ci) * KT + u));
+                            j4 = __ldcg(reinterpret_cast<const int4*>(a.cand_idx + ((size_t)rr * nc + ci) * KT + u));
+                        }
+                        xv[u] = v4.x; xv[u + 1] = v4.y; xv[u + 2] = v4.z; xv[u + 3] = v4.w;
+                        xj[u] = j4.x; xj[u + 1] = j4.y; xj[u + 2] = j4.z; xj[u + 3] = j4.w;
+                    }
+    #pragma unroll
+                    for (int u = 0; u < KT; ++u) {
+                        unsigned q = __ballot_sync(0xffffffffu, xj[u] >= 0 && xv[u] >= thr && xv[u] > -INFINITY);
+                        while (q != 0u) {
+                            const int src = __ffs(q) - 1;
+                            q &= q - 1;
+                            const float cx = __shfl_sync(0xffffffffu, xv[u], src);
+                            const int cxi = __shfl_sync(0xffffffffu, xj[u], src);
+                            const unsigned bet = __ballot_sync(0xffffffffu, better(lv, li, cx, cxi)) & ((1u << KT) - 1u);
+                            const int pos = __popc(bet);
+                            const float uv = __shfl_up_sync(0xffffffffu, lv, 1);
+                            const int ui = __shfl_up_sync(0xffffffffu, li, 1);
+                            if (lane < KT) {
+                                if (lane == pos) { lv = cx; li = cxi; }
+                                else if (lane > pos) { lv = uv; li = ui; }
+                            }
+                            thr = __shfl_sync(0xffffffffu, lv, KT - 1);
+                        }
                     }
                 }
             }
