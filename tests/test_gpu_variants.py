@@ -1,0 +1,35 @@
+"""Kernel variants that the library picks by launch size or by an opt-in switch, forced through their environment switch
+in a child process (the switches are read once per process) so the small parity cases cover them too:
+ * ITB_ATTN_STAGE=32 -- the 32-position / 4-CTAs-per-SM build of the tensor-core attention kernel, which the library
+   only selects for launches of more than ~2 waves (4096 beam rows); ITB_ATTN_STAGE=64 is the small-launch build;
+ * ITB_VOCAB_PAIR=1 -- the CTA-pair (tcgen05 cta_group::2) launch of the fused vocabulary projection."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(env, select, path="tests/test_gpu_kernels.py"):
+    e = dict(os.environ)
+    e.update(env)
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "-p", "no:cacheprovider", path, "-k", select],
+                       cwd=ROOT, env=e, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout and "no tests ran" not in r.stdout, r.stdout[-500:]
+
+
+@pytest.mark.parametrize("stage", ["32", "64"])
+def test_attention_kernels_in_both_staging_builds(stage):
+    _run({"ITB_ATTN_STAGE": stage}, "attention")
+
+
+def test_decode_parity_with_the_many_wave_attention_build():
+    _run({"ITB_ATTN_STAGE": "32"}, "16bit or forward_many or encoder", path="tests/test_gpu_decode.py")
+
+
+def test_fused_vocab_projection_on_cta_pairs():
+    _run({"ITB_VOCAB_PAIR": "1"}, "fused_vocab")
