@@ -97,8 +97,11 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
     extern __shared__ __align__(16) unsigned char am_smem[];
     unsigned char* ws = am_smem + (size_t)(threadIdx.x >> 5) * (STAGE * AM_ROWB);
     const uint32_t ws_u32 = (uint32_t)__cvta_generic_to_shared(ws);
-    const int part = lane & 15;                                     // 16-byte piece of the 256-byte row this lane copies
-    const size_t part_off = (part < 8) ? (size_t)part * 8 : (size_t)d + (size_t)(part - 8) * 8;
+    // copies: one cp.async instruction moves the K (or the V) halves of 4 rows, 8 lanes x 16 bytes per row.  K and V of a
+    // stage travel as two cp.async groups, so that the K half of the buffer can be refilled as soon as the scores are
+    // done and the V half as soon as P.V is done (software pipeline over the stages, see the main loop)
+    const int piece = lane & 7, rsub = lane >> 3;
+    const uint32_t lane_dst = ws_u32 + rsub * AM_ROWB + piece * 16;
     // Cross-attention: the encoder-side K,V and the source mask were written once per batch, many launches ago, and
     // their addresses depend on the warp index only.  The first stage is therefore requested BEFORE the wait on the
     // predecessor grid and before the control words are known (rows past the source length are fetched too and
@@ -109,15 +112,18 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
         const T* cbase = reinterpret_cast<const T*>(a.kv) + ((size_t)b * a.S * a.L + a.layer) * 2 * d + hoff;
         const size_t cstride = (size_t)a.L * 2 * d;
 #pragma unroll
-        for (int k = 0; k < STAGE / 2; ++k) {
-            const int row = 2 * k + (lane >> 4);
-            if ((row & ~31) < a.S) {
-                const bool ok = row < a.S;
-                const T* src = cbase + (ok ? (size_t)row * cstride + part_off : (size_t)0);
-                const uint32_t dst = ws_u32 + row * AM_ROWB + part * 16;
-                const int nbytes = ok ? 16 : 0;
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nbytes) : "memory");
+        for (int kv = 0; kv < 2; ++kv) {                              // group 0: K halves, group 1: V halves
+#pragma unroll
+            for (int k = 0; k < STAGE / 4; ++k) {
+                const int row = 4 * k + rsub;
+                if ((row & ~31) < a.S) {
+                    const bool ok = row < a.S;
+                    const T* src = cbase + (ok ? (size_t)row * cstride + (size_t)kv * d + piece * 8 : (size_t)0);
+                    const int nbytes = ok ? 16 : 0;
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(lane_dst + 4 * k * AM_ROWB + kv * 128), "l"(src), "r"(nbytes) : "memory");
+                }
             }
+            asm volatile("cp.async.commit_group;" ::: "memory");
         }
 #pragma unroll
         for (int hv = 0; hv < AM_NCH; ++hv) {
@@ -237,12 +243,11 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
     // costs a shuffle, one wide multiply-add and the cp.async
     constexpr uint32_t kNoRow = 0xFFFFFFFFu;
     const uint32_t stride16 = (uint32_t)(pos_stride * sizeof(T) / 16);
-    const unsigned char* lane_src = reinterpret_cast<const unsigned char*>(base + part_off);
-    const uint32_t lane_dst = ws_u32 + (lane >> 4) * AM_ROWB + part * 16;
-    for (int sb = 0; sb < nv; sb += STAGE) {
-        // ---- virtual positions sb + 32*hv + lane: row index and meta = owner mask (bits 0-3) | masked-source (bit 4) ----
-        uint32_t rowidx[AM_NCH];                                     // row offset in 16-byte units, kNoRow = absent
-        int meta[AM_NCH];
+    const unsigned char* lane_src = reinterpret_cast<const unsigned char*>(base) + piece * 16;
+    const size_t v_off = (size_t)d * sizeof(T);                      // V half of a cache row, in bytes
+
+    // virtual positions sb + 32*hv + lane: row offset and meta = owner mask (bits 0-3) | masked-source (bit 4)
+    auto build_list = [&](int sb, uint32_t (&rowidx)[AM_NCH], int (&meta)[AM_NCH]) {
 #pragma unroll
         for (int hv = 0; hv < AM_NCH; ++hv) {
             rowidx[hv] = kNoRow; meta[hv] = 0;
@@ -260,26 +265,46 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
                 if (tail && p == n - 1) slot = q0 + qi;                          // the row appended above
                 if (in) { rowidx[hv] = (uint32_t)((b * a.beam + slot) * a.T_max + p) * stride16; meta[hv] = tail ? (1 << qi) : 0xF; }
             } else if (v < nv) {
-                {
-                    rowidx[hv] = (uint32_t)v * stride16;
-                    const int mk = (sb == 0) ? mk0[hv] : ((mrow != nullptr) ? (int)mrow[v] : 1);
-                    meta[hv] = 0xF | ((mk == 0) ? 0x10 : 0);
-                }
+                rowidx[hv] = (uint32_t)v * stride16;
+                const int mk = (sb == 0) ? mk0[hv] : ((mrow != nullptr) ? (int)mrow[v] : 1);
+                meta[hv] = 0xF | ((mk == 0) ? 0x10 : 0);
             }
         }
-        const int nchunk = min(AM_NCH, (nv - sb + 31) >> 5);         // 32-position chunks in this stage (warp-uniform)
+    };
+    // one cp.async group: the K (kv = 0) or V (kv = 1) halves of the rows of a stage's first `nch` chunks
+    auto issue_half = [&](const uint32_t (&rowidx)[AM_NCH], int nch, int kv) {
 #pragma unroll
-        for (int k = 0; k < STAGE / 2; ++k) {
-            if (k < 16 * nchunk && (SELF || sb != 0)) {              // cross: stage 0 was requested at the top
-                const uint32_t o = __shfl_sync(0xffffffffu, rowidx[k >> 4], (2 * k + (lane >> 4)) & 31);
+        for (int k = 0; k < STAGE / 4; ++k) {
+            if (k < 8 * nch) {
+                const uint32_t o = __shfl_sync(0xffffffffu, rowidx[k >> 3], (4 * k + rsub) & 31);
                 const bool ok = o != kNoRow;
-                const unsigned char* src = lane_src + (size_t)(ok ? o : 0u) * 16;
+                const unsigned char* src = lane_src + (size_t)(ok ? o : 0u) * 16 + (kv != 0 ? v_off : (size_t)0);
                 const int nbytes = ok ? 16 : 0;
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(lane_dst + 2 * k * AM_ROWB), "l"(src), "r"(nbytes) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(lane_dst + 4 * k * AM_ROWB + kv * 128), "l"(src), "r"(nbytes) : "memory");
             }
         }
-        asm volatile("cp.async.wait_all;" ::: "memory");
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    // ---- software pipeline over the stages.  Groups are committed in the order K0 V0 K1 V1 ...; K(s+1) is requested
+    //      right after the last scores of stage s (the K half is free then), V(s+1) after its last P.V, so a warp keeps
+    //      copies in flight while it computes.  The position list of stage s+1 is built at the top of stage s. ----
+    uint32_t rowidx[AM_NCH], rowidx_n[AM_NCH];
+    int meta[AM_NCH], meta_n[AM_NCH];
+    build_list(0, rowidx, meta);
+    if (SELF) {                                                       // cross: stage 0 was requested at the top
+        const int nch0 = min(AM_NCH, (nv + 31) >> 5);
+        issue_half(rowidx, nch0, 0);
+        issue_half(rowidx, nch0, 1);
+    }
+    for (int sb = 0; sb < nv; sb += STAGE) {
+        const int nchunk = min(AM_NCH, (nv - sb + 31) >> 5);         // 32-position chunks in this stage (warp-uniform)
+        const bool has_next = sb + STAGE < nv;
+        const int nchunk_n = min(AM_NCH, (nv - sb - STAGE + 31) >> 5);
+        if (has_next) build_list(sb + STAGE, rowidx_n, meta_n);
+        asm volatile("cp.async.wait_group 1;" ::: "memory");        // K of this stage has landed (V may still be in flight)
         __syncwarp();
+        bool k_next = false;
 
 #pragma unroll
         for (int cb = 0; cb < AM_NCH; ++cb) {
@@ -332,6 +357,16 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
 #pragma unroll
                     for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= corr; o[nt][1] *= corr; o[nt][2] *= corr; o[nt][3] *= corr; }
                 }
+                if (cb == nchunk - 1 && has_next) {          // the K half is free: request K of the next stage
+                    __syncwarp();
+                    issue_half(rowidx_n, nchunk_n, 0);
+                    k_next = true;
+                }
+                if (cb == 0) {                               // V of this stage (everything older than the group just issued)
+                    if (k_next) asm volatile("cp.async.wait_group 1;" ::: "memory");
+                    else asm volatile("cp.async.wait_group 0;" ::: "memory");
+                    __syncwarp();
+                }
                 // ---- O += P.V : rows 16t + {2c, 2c+1, 2c+8, 2c+9}, dims [8nl, 8nl+8) ----
 #pragma unroll
                 for (int t = 0; t < 2; ++t) {
@@ -350,8 +385,14 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
                 }
             }
         }
-        __syncwarp();                    // the stage buffer is rewritten by the next iteration
+        __syncwarp();                    // the V half is free: request V of the next stage
+        if (has_next) {
+            issue_half(rowidx_n, nchunk_n, 1);
+#pragma unroll
+            for (int hv = 0; hv < AM_NCH; ++hv) { rowidx[hv] = rowidx_n[hv]; meta[hv] = meta_n[hv]; }
+        }
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");     // nothing may stay in flight (empty position lists)
     // ---- normalise and store: lane (nl < nq, c) holds dims [16c,16c+16) of row nl ----
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
