@@ -104,4 +104,10 @@ total += L * bench("cross_attn S=%d" % S, lambda i: _lib.check(lib.itb_cross_att
                                                                                         i % L, _lib.ptr(mask), _lib.ptr(ctx), M, beam, d, H,
                                                                                         S, L, st())),
                    bytes_alg=B * S * 2 * d * esz, nbuf=NB)
+# the same bytes with one layer per buffer (rows 3 KB apart instead of L x 3 KB): what a layer-major cross-KV layout would give
+ckv1 = [rnd(B, S, 1, 2, d, dt=ACT) for _ in range(L)]
+bench("cross_attn S=%d, layer-major rows" % S, lambda i: _lib.check(lib.itb_cross_attention(DT, _lib.ptr(ctl), None, None, _lib.ptr(qkv), 3 * d,
+                                                                                             _lib.ptr(ckv1[i % L]), 0, _lib.ptr(mask), _lib.ptr(ctx),
+                                                                                             M, beam, d, H, S, 1, st())),
+      bytes_alg=B * S * 2 * d * esz, nbuf=NB)
 print("sum over one search step (6 layers + vocab GEMM, without embed / beam kernel): %.1f us" % total)
