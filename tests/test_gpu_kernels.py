@@ -173,9 +173,11 @@ def test_embed_ln_and_add_ln(dtype):
 
 # ------------------------------------------------------------------------------------------------ attention
 @pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16, _lib.F16])
-@pytest.mark.parametrize("step", [1, 2, 40])
-def test_self_attention_through_ancestor_table(dtype, step):
-    B, beam, d, H, T = 3, 4, 768, 12, 48
+@pytest.mark.parametrize("step,T,beam", [(1, 48, 4), (2, 48, 4), (40, 48, 4), (9, 12, 4), (120, 130, 4), (70, 80, 5)])
+def test_self_attention_through_ancestor_table(dtype, step, T, beam):
+    """T = 12: ancestor table shorter than a warp; step 120: up to 480 virtual positions (many copy stages, table reads
+    past the 32 positions held in registers); beam 5: a second group of one slot per sentence."""
+    B, d, H = 3, 768, 12
     M, pc = B * beam, step - 1
     act = ACT[dtype]
     qkv = _rand((M, 3 * d), 11)
@@ -214,8 +216,11 @@ def test_self_attention_through_ancestor_table(dtype, step):
 
 @pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16, _lib.F16])
 @pytest.mark.parametrize("masked", [False, True])
-def test_cross_attention_with_additive_mask(dtype, masked):
-    B, beam, d, H, S, L, layer = 3, 4, 768, 12, 21, 2, 1
+@pytest.mark.parametrize("S,beam", [(21, 4), (100, 4), (77, 5)])
+def test_cross_attention_with_additive_mask(dtype, masked, S, beam):
+    """S = 100 / 77: several copy stages with a partial last chunk (the K / V pipeline of the tensor-core kernel);
+    beam 5: a second group of one slot per sentence."""
+    B, d, H, L, layer = 3, 768, 12, 2, 1
     M = B * beam
     act = ACT[dtype]
     q = _rand((M, 3 * d), 21)
