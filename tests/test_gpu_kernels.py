@@ -60,7 +60,8 @@ def test_linear_fp16(impl, M, N, K):
 
 @pytest.mark.parametrize("dtype", [_lib.BF16, _lib.F16], ids=["bf16", "fp16"])
 @pytest.mark.parametrize("rows,V,beam", [(5, 300, 4), (130, 1000, 3), (244, 60000, 4), (40, 5003, 8), (33, 777, 12), (260, 4096, 1),
-                                         (700, 3000, 5), (520, 1500, 4), (1024, 2200, 4)])
+                                         (700, 3000, 5), (520, 1500, 4), (1024, 2200, 4),
+                                         (4096, 60000, 4)])      # last: the bench's full size (BASELINE configs[1])
 def test_fused_vocab_projection_partials(dtype, rows, V, beam):
     """itb_vocab_partials: per-chunk max / sum-exp / top-KT emitted by the GEMM epilogue reproduce log_softmax's
     log-sum-exp and the row top-k (value desc, index asc) of the full logits; the optional logits output equals the GEMM."""
