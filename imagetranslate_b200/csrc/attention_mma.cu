@@ -413,12 +413,11 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
 template <typename T, int STAGE>
 static int launch_attn_mma_stage(const AttnMmaArgs& a, bool self, cudaStream_t s) {
     const dim3 grid((a.n_warps + AM_WARPS - 1) / AM_WARPS), block(AM_THREADS);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e1 = cudaFuncSetAttribute(attn_mma_kernel<T, true, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, AM_SMEM(STAGE));
-        cudaError_t e2 = cudaFuncSetAttribute(attn_mma_kernel<T, false, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, AM_SMEM(STAGE));
+    static bool attr_self[ITB_MAX_DEVICES] = {}, attr_cross[ITB_MAX_DEVICES] = {};
+    {
+        cudaError_t e1 = itb_smem_attr_once(attr_self, attn_mma_kernel<T, true, STAGE>, AM_SMEM(STAGE));
+        cudaError_t e2 = itb_smem_attr_once(attr_cross, attn_mma_kernel<T, false, STAGE>, AM_SMEM(STAGE));
         if (e1 != cudaSuccess || e2 != cudaSuccess) { itb_set_error("attention: cudaFuncSetAttribute failed"); return -1; }
-        attr_set = true;
     }
     cudaError_t e = self ? itb_launch(attn_mma_kernel<T, true, STAGE>, grid, block, (size_t)AM_SMEM(STAGE), s, a)
                          : itb_launch(attn_mma_kernel<T, false, STAGE>, grid, block, (size_t)AM_SMEM(STAGE), s, a);
@@ -437,7 +436,7 @@ static int launch_attn_mma(AttnMmaArgs a, bool self, cudaStream_t s) {
         const char* e = getenv("ITB_ATTN_STAGE");
         forced = (e != nullptr) ? atoi(e) : 0;
     }
-    const bool small_stage = forced != 0 ? forced == 32 : a.n_warps > 2 * 148 * 12;
+    const bool small_stage = forced != 0 ? forced == 32 : a.n_warps > 2 * itb_num_sms() * 12;
     return small_stage ? launch_attn_mma_stage<T, 32>(a, self, s) : launch_attn_mma_stage<T, 64>(a, self, s);
 }
 

@@ -870,16 +870,7 @@ int itb_make_tmap_16b(CUtensorMap* map, const void* base, int rows, int K, int b
 
 
 
-static int num_sms() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-        if (n <= 0) n = 148;
-    }
-    return n;
-}
+static int num_sms() { return itb_num_sms(); }
 
 // Tile plan.  The decode GEMMs are weight-streaming and latency-bound at small M, so the activation rows per tile
 // (UMMA N = mt) and the split-K factor are chosen to spread the weight matrix over as many SMs as possible:
@@ -913,11 +904,10 @@ static int launch_tc(const CUtensorMap& tmW, const CUtensorMap& tmA, const ItbCt
                      int M, int N, int K, int ldo, int act_f16, int nsplit, cudaStream_t s, const TcVocabPart vp = TcVocabPart()) {
     constexpr int kSmem = TcCfg<MT>::kSmemBytes + (EPI == ITB_EPI_VOCAB_K4 ? TC_CAND_SLOTS * 32 * TC_VOC_EPI_WARPS * 4 : 0);   // + candidate buffer
     constexpr int kThreads = EPI == ITB_EPI_VOCAB_K4 ? TC_VOC_THREADS : TC_THREADS;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+    static bool attr_set[ITB_MAX_DEVICES] = {};
+    {
+        cudaError_t e = itb_smem_attr_once(attr_set, gemm_tc_kernel<MT, EPI>, kSmem);
         if (e != cudaSuccess) { itb_set_error("gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return -1; }
-        attr_set = true;
     }
     const int total = ((N + TC_BN - 1) / TC_BN) * ((M + MT - 1) / MT) * nsplit;
     const int grid = total < num_sms() ? total : num_sms();
@@ -958,11 +948,10 @@ int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const v
 template <int KT>
 static int launch_tc2_vocab(const CUtensorMap& tmX, const CUtensorMap& tmWv128, const ItbCtl* ctl, const float* bias, int rows, int V,
                             int K, int act_f16, cudaStream_t s, const TcVocabPart& vp) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc2_vocab_kernel<KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM);
+    static bool attr_set[ITB_MAX_DEVICES] = {};
+    {
+        cudaError_t e = itb_smem_attr_once(attr_set, gemm_tc2_vocab_kernel<KT>, TC2_SMEM);
         if (e != cudaSuccess) { itb_set_error("gemm_tc2: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return -1; }
-        attr_set = true;
     }
     const int total = ((rows + 255) / 256) * ((V + 255) / 256);
     const int cap = num_sms() & ~1;

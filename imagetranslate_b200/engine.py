@@ -8,7 +8,9 @@ Data layout in HBM (all allocated once per engine and reused across batches; ker
   kv_self    [L][M][T][2][d]      self-attention KV cache, M = B*beam rows; NEVER reordered: the beam kernel
                                   maintains anc[M][T] (which beam slot physically holds position p)
   tokens/anc/scores/sizes/fin     ping-pong search state written by the fused beam kernel
-  logits     [M][V4] fp32         the only (M,V)-sized tensor; written by the vocab GEMM, read once
+  cand_*, chunk_*                 per (row, 128-entry vocabulary chunk) max / sum-exp / top-K written by the fused vocabulary
+                                  GEMM epilogue (16-bit modes): no (M,V) tensor exists in HBM
+  logits     [M][V4] fp32         fp32 parity mode and parity traces only (written once by the CUDA-core GEMM, read once)
 """
 import ctypes as C
 
@@ -25,6 +27,12 @@ def _lin(mod):
 
 
 _UID = [0]
+
+
+def _src_key(tensors):
+    """What a packed copy depends on: in-place updates bump `_version`; `model.half()` / `.bfloat16()` / `.to(device)` swap
+    `param.data` WITHOUT bumping it, so storage address, dtype and device are part of the key too."""
+    return tuple((t._version, t.data_ptr(), t.dtype, str(t.device)) for t in tensors)
 
 
 class PackedDecoder(object):
@@ -88,10 +96,10 @@ class PackedDecoder(object):
         self.b_ckv = torch.cat(ckv_b, 0).to(device, torch.float32).contiguous()
         self.w_vocab, self.b_vocab = mat(output_layer.layer.weight), f32(output_layer.layer.bias)
         self.V = self.w_vocab.shape[0]
-        self.versions = tuple(t._version for t in self._src)
+        self.versions = _src_key(self._src)
 
     def stale(self):
-        return tuple(t._version for t in self._src) != self.versions
+        return _src_key(self._src) != self.versions
 
 
 class PackedEncoder(object):
@@ -136,10 +144,10 @@ class PackedEncoder(object):
                 w_1=mat(ly.intermediate.dense.weight), b_1=f32(ly.intermediate.dense.bias),
                 w_2=mat(ly.output.dense.weight), b_2=f32(ly.output.dense.bias),
                 ln2_g=f32(ly.output.LayerNorm.weight), ln2_b=f32(ly.output.LayerNorm.bias)))
-        self.versions = tuple(t._version for t in self._src)
+        self.versions = _src_key(self._src)
 
     def stale(self):
-        return tuple(t._version for t in self._src) != self.versions
+        return _src_key(self._src) != self.versions
 
 
 class Workspace(object):

@@ -203,7 +203,10 @@ class Seq2Seq(nn.Module):
                 if tie_embed:
                     dec.embeddings.position_embeddings = ee.position_embeddings
                 self.output_layer[i].weight = dec.embeddings.word_embeddings.weight     # :75 (wrapper alias, see above)
-                dec.embeddings.token_type_embeddings.weight = ee.token_type_embeddings.weight
+                # :76-77 _tie_or_clone_weights(out=encoder..., inp=dec...) sets out.weight = inp.weight: the ENCODER's
+                # table is re-pointed at each decoder's in turn, so it ends up shared with the LAST decoder only and
+                # every other decoder keeps its own (deep-copied) token-type table.
+                ee.token_type_embeddings.weight = dec.embeddings.token_type_embeddings.weight
 
     def encode(self, src_inputs, src_mask, src_langs, images=None):
         dev = self.encoder.embeddings.word_embeddings.weight.device

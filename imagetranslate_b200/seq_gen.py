@@ -51,6 +51,7 @@ class BeamDecoder(nn.Module):
         self._lane = threading.local()      # forward_many: which engine (workspace + stream) this thread drives
         self._lock = threading.Lock()
         self.kernel_launches = 0            # kernels enqueued by this decoder so far (bench.py's gpu_launches)
+        self.trace = None                   # parity hook: a list here receives the per-step state (one host sync per step)
         # forward_many packs consecutive batches into one super-batch while their memory lengths stay within this ratio
         # (rows of the shorter batches idle once their own search has ended)
         self.pack_ratio = float(os.environ.get("ITB_PACK_RATIO", "1.5"))
@@ -176,8 +177,10 @@ class BeamDecoder(nn.Module):
         if src_inputs is None:
             max_lens = torch.full((B,), int(max_len), dtype=torch.int64)
         else:
-            # :121 -- same IEEE double arithmetic as python's int(a * s + b), on whatever device src_sizes lives
-            max_lens = (src_sizes.to(torch.float64) * self.max_len_a + self.max_len_b).to(torch.int64).clamp(max=n_pos)
+            # :121 maps max_len_func over the ELEMENTS of the src_sizes LongTensor: `max_len_a * <0-dim int tensor>` is a
+            # float32 tensor (python-scalar promotion), `+ max_len_b` stays float32, int() truncates.  float32, not double:
+            # at a = 1.3 the two differ for s = 90, 170, 180, ... (float32 gives 121 for s = 90, double 122).
+            max_lens = (src_sizes.to(torch.float32) * self.max_len_a + self.max_len_b).to(torch.int64).clamp(max=n_pos)
         max_len = min(int(max_len), n_pos)
         code = self._dtype_code(wemb)
         return dict(memory=memory, src_mask=mem_mask, first_tokens=first_tokens, tgt_type_ids=tgt_langs, max_lens=max_lens,
@@ -190,22 +193,32 @@ class BeamDecoder(nn.Module):
         g0 = groups[0]
         eng = self._engine(g0["device"], g0["code"])
         pw = self._weights(g0["model"], g0["lang"], g0["code"], g0["device"])
-        res = eng.decode_groups(pw, groups, g0["beam"], g0["pad"], g0["eos"], float(self.len_penalty_ratio))
+        res = eng.decode_groups(pw, groups, g0["beam"], g0["pad"], g0["eos"], float(self.len_penalty_ratio), trace=self.trace)
         with self._lock:
             self.kernel_launches += eng.last_steps * eng.launches_per_step + 4
         outs = []
         for g, (tok, lens, lens_full) in zip(groups, res):
             tok = tok.to(torch.int64)
             sel = (lens if g["unpad"] else lens_full).tolist()
-            outs.append([tok[r, :sel[r]].clone() for r in range(g["B"])])
+            outs.append([tok[r, :n] for r, n in enumerate(sel)])       # views of this call's own fresh CPU tensor
         return outs
 
     def forward(self, src_inputs=None, src_sizes=None, first_tokens=None, src_mask=None, src_langs=None, tgt_langs=None,
                 pad_idx=None, max_len: int = None, unpad_output: bool = True, beam_width: int = None, images=None,
                 proposals=None, image_embed=None):
-        g = self._prepare(src_inputs, src_sizes, first_tokens, src_mask, src_langs, tgt_langs, pad_idx, max_len, unpad_output,
-                          beam_width, images, proposals, image_embed)
-        return self._decode_groups([g])[0]
+        # the model's device becomes the thread's current device for the call (function attributes, graph capture and plain
+        # launches all act on the CURRENT device; DataParallel's worker threads set it, a plain caller may not have)
+        with torch.cuda.device(self._model_device()):
+            g = self._prepare(src_inputs, src_sizes, first_tokens, src_mask, src_langs, tgt_langs, pad_idx, max_len, unpad_output,
+                              beam_width, images, proposals, image_embed)
+            return self._decode_groups([g])[0]
+
+    def _model_device(self):
+        model = self.seq2seq_model.module if hasattr(self.seq2seq_model, "module") else self.seq2seq_model
+        device = model.encoder.embeddings.word_embeddings.weight.device
+        if device.type != "cuda":
+            raise RuntimeError("imagetranslate_b200.BeamDecoder needs the model on a CUDA device (no CPU fallback)")
+        return device
 
     # ------------------------------------------------------------------ several batches in flight
     @staticmethod
@@ -254,6 +267,10 @@ class BeamDecoder(nn.Module):
         device = wemb.device
         if device.type != "cuda":
             raise RuntimeError("imagetranslate_b200.BeamDecoder needs the model on a CUDA device (no CPU fallback)")
+        with torch.cuda.device(device):
+            return self._forward_many(batches, lanes, rows, model, wemb, device)
+
+    def _forward_many(self, batches, lanes, rows, model, wemb, device):
         packs = self._pack(batches, max(int(rows), 1))
         results = [None] * len(batches)
 

@@ -25,17 +25,29 @@ CASES = {
     # wide beam, (not lang_dec) and tie_embed => single output layer module (src/seq2seq.py:54-59)
     "text_b8_tie": dict(kind="text", V=900, enc=1, dec=1, lang_dec=False, tie=True, B=2, S=10, beam=8, seed=15,
                         eos_bias=0.7),
+    # real size (BASELINE configs[1] model: MassSeq2Seq base 6+6, d 768, V 60000), S = 64 ragged; the loop bound is set
+    # explicitly so the full-prefix reference finishes in seconds on CPU.  Fixture also holds per-step log-probs.
+    "real_6x6": dict(kind="text", V=60000, enc=6, dec=6, lang_dec=False, tie=False, B=4, S=64, beam=4, seed=16,
+                     eos_bias=0.0, max_len=20, min_len=40, record=True),
+    # src_sizes 90 and 170 at max_len_a = 1.3: the reference computes max_lens in float32 on tensor elements
+    # (src/seq_gen.py:113-121), which gives 121 / 225 where double arithmetic gives 122 / 226.  No EOS => output length
+    # = max_lens[r], and the over-length zeroing / forced PAD (:138-139,197,207) start at that step.
+    "text_maxlens_f32": dict(kind="text", V=500, enc=1, dec=1, lang_dec=False, tie=False, B=3, S=180, beam=2, seed=17,
+                             eos_bias=-30.0, lens=[180, 90, 170]),
 }
 
 GEN = dict(max_len_a=1.3, max_len_b=5, len_penalty_ratio=0.8)   # src/translate.py:26-28 defaults
 
 
-def make_text_batch(B, S, V, seed, min_len=4):
+def make_text_batch(B, S, V, seed, min_len=4, lens=None):
     """Synthetic padded source batch in MTDataset's format (src/dataset.py:141-163):
     row = <lang 5> body </s 4> pad 0...; pad_idx = first pad position, or S-1 when none."""
     g = torch.Generator().manual_seed(seed)
-    lens = torch.randint(min_len, S + 1, (B,), generator=g)
-    lens[0] = S
+    if lens is None:
+        lens = torch.randint(min_len, S + 1, (B,), generator=g)
+        lens[0] = S
+    else:
+        lens = torch.tensor(lens)
     src = torch.zeros(B, S, dtype=torch.long)
     for b in range(B):
         n = int(lens[b])
@@ -62,8 +74,10 @@ def build(name):
     kw = dict(first_tokens=torch.full((B,), 6, dtype=torch.long), tgt_langs=torch.full((B,), tgt, dtype=torch.long),
               pad_idx=0, beam_width=c["beam"])
     if c["kind"] == "text":
-        src, mask, pad_idx = make_text_batch(B, c["S"], c["V"], c["seed"] + 1000)
+        src, mask, pad_idx = make_text_batch(B, c["S"], c["V"], c["seed"] + 1000, c.get("min_len", 4), c.get("lens"))
         kw.update(src_inputs=src, src_mask=mask, src_sizes=pad_idx, src_langs=torch.zeros(B, dtype=torch.long))
+        if "max_len" in c:
+            kw.update(max_len=c["max_len"])
     else:
         g = torch.Generator().manual_seed(c["seed"] + 2000)
         kw.update(image_embed=torch.randn(B, c["S"], 768, generator=g), max_len=c["max_len"])

@@ -51,7 +51,20 @@ def load():
         exec(compile(src, seq_gen.__file__, "exec"), seq_gen.__dict__)
         sys.modules["seq_gen"] = seq_gen
 
-        ns = types.SimpleNamespace(seq_gen=seq_gen)
+        # Recorder: the same file with ONE extra statement after `top_beam_scores = top_scores`
+        # (src/seq_gen.py:227) that appends clones of the step's tensors to the module-level list TRACE.  `output` is the
+        # (M,V) log-softmax AFTER the finished / over-length rows were zeroed (:194-197).
+        hook = "            top_beam_scores = top_scores\n"
+        assert src.count(hook) == 1
+        rec_src = src.replace(hook, hook + "            TRACE.append(dict(i=i, log_probs=output.clone(), prefixes=top_beam_outputs.clone(), "
+                              "scores=top_scores.clone(), raw_idx=indices.clone(), "
+                              "sizes=None if cur_size is None else cur_size.clone()))\n")
+        seq_gen_rec = types.ModuleType("seq_gen_rec")
+        seq_gen_rec.__file__ = seq_gen.__file__
+        seq_gen_rec.TRACE = []
+        exec(compile(rec_src, seq_gen.__file__, "exec"), seq_gen_rec.__dict__)
+
+        ns = types.SimpleNamespace(seq_gen=seq_gen, seq_gen_rec=seq_gen_rec)
         for name in ("bert_seq2seq", "seq2seq", "mass_seq2seq", "dataset"):
             setattr(ns, name, importlib.import_module(name))
     finally:

@@ -135,7 +135,7 @@ def test_16bit_teacher_forced_logprob_error(mode, gemm_impl):
     """north_star tolerance: per-step log-prob within 1e-2 abs of the fp32 reference (bf16 weights on both sides)."""
     worst, worst_top, agree, total = _teacher_forced(mode, gemm_impl, 2)
     print("%s teacher-forced: max |dlogp| vocab %.3e, top-8 %.3e, top-1 agreement %d/%d" % (mode, worst, worst_top, agree, total))
-    assert worst_top <= 1e-2 and worst <= (1e-2 if mode == "fp16" else 2e-2)
+    assert worst_top <= 1e-2 and worst <= 1e-2
 
 
 def test_16bit_six_layer_decoder_error_and_stepwise_agreement():
@@ -145,9 +145,8 @@ def test_16bit_six_layer_decoder_error_and_stepwise_agreement():
         worst, worst_top, agree, total = _teacher_forced(mode, _lib.GEMM_AUTO, 6, seed=43, V=8000, B=12, S=20)
         print("6-layer %s: max |dlogp| vocab %.3e, top-8 %.3e, top-1 agreement %d/%d = %.4f" % (
             mode, worst, worst_top, agree, total, agree / total))
-        assert worst_top <= 1e-2
-        if mode == "fp16":
-            assert agree >= 0.99 * total
+        assert worst_top <= 1e-2 and worst <= 1e-2
+        assert agree >= 0.99 * total
 
 
 @pytest.mark.parametrize("mode", ["bf16", "fp16"])
