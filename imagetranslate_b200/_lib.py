@@ -12,7 +12,7 @@ LIB_PATH = os.environ.get("ITB_LIB") or os.path.join(_HERE, "libitb.so")      # 
 F32, BF16, F16 = 0, 1, 2      # (weights, activations): (f32,f32) / (bf16,bf16) / (fp16,fp16); include/itb.h
 GEMM_AUTO, GEMM_SIMT, GEMM_TCGEN05 = 0, 1, 2
 EPI_BIAS_F32, EPI_BIAS_GELU_ACT, EPI_BIAS_ACT = 0, 1, 2
-ABI_VERSION = 3
+ABI_VERSION = 4
 Y_PARTIALS = 4
 
 P = C.c_void_p
@@ -41,7 +41,13 @@ class Config(C.Structure):
         + [("G", C.c_int), ("reserved1", C.c_int)]
         + [(n, P) for n in ("src_mask", "cross_kv", "ctl", "tokens", "anc", "scores",
                             "sizes", "fin", "kv_self", "x_f32", "x_act", "qkv", "ctx", "y", "ffn_h", "logits",
-                            "cand_val", "cand_idx", "chunk_max", "chunk_sum", "sent_counter")])
+                            "cand_val", "cand_idx", "chunk_max", "chunk_sum", "sent_counter")]
+        + [("two_stream", C.c_int), ("S2", C.c_int)]
+        + [(n, P) for n in ("layers2_host", "emb2_word", "emb2_pos", "emb2_type", "emb2_ln_g", "emb2_ln_b", "cross_kv2",
+                            "src_mask2", "mem_len2", "kv_self2", "stream_gate", "x_first")]
+        + [("n_prop", C.c_int), ("reserved2", C.c_int)]
+        + [(n, P) for n in ("proposals", "prop_emb", "lex_gate", "lex_ln_g", "lex_ln_b")]
+        + [("lex_ln_eps", C.c_float), ("gate_eps", C.c_float)])
 
 
 _SIGS = {
@@ -59,6 +65,9 @@ _SIGS = {
     "itb_self_attention": (C.c_int, [C.c_int, P, P, P, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, P]),
     "itb_cross_attention": (C.c_int, [C.c_int, P, P, P, P, C.c_int, P, C.c_int, P, P, C.c_int, C.c_int, C.c_int, C.c_int,
                                       C.c_int, C.c_int, P]),
+    "itb_save_state": (C.c_int, [P, P, P, C.c_int, C.c_int, P]),
+    "itb_gate_mix": (C.c_int, [C.c_int, P, P, P, C.c_float, P, P, C.c_int, C.c_int, P]),
+    "itb_attend_proposal": (C.c_int, [C.c_int, P, P, C.c_int, C.c_int, P, P, P, P, C.c_float, P, P, C.c_int, C.c_int, C.c_int, P]),
     "itb_beam_step": (C.c_int, [C.POINTER(Config), P]),
     "itb_finalize": (C.c_int, [P, P, P, P, P, C.c_int, P, P, P, C.c_int, C.c_int, C.c_int, P]),
     "itb_init_state": (C.c_int, [C.POINTER(Config), P, P, P]),

@@ -79,10 +79,32 @@ static Linear make_linear(const void* A, const void* W, const float* bias, void*
     return l;
 }
 
-struct itb_decoder {
-    itb_config cfg;
+// One decoder layer stack: its weights and the six linears of every layer with their cached TMA descriptors.
+struct LayerSet {
     std::vector<itb_layer> layers;
     std::vector<Linear> qkv, o, cq, co, f1, f2;
+    int build(const itb_config* c, const itb_layer* src) {
+        const int M = c->B * c->beam, D = c->d, F = c->F;
+        layers.assign(src, src + c->L);
+        int r = 0;
+        for (int l = 0; l < c->L && r == 0; ++l) {
+            const itb_layer& w = layers[l];
+            qkv.push_back(make_linear(c->x_act, w.w_qkv, w.b_qkv, c->qkv, M, 3 * D, D, 3 * D, ITB_EPI_BIAS_F32));
+            o.push_back(make_linear(c->ctx, w.w_o, w.b_o, c->y, M, D, D, D, ITB_EPI_BIAS_F32, ITB_Y_PARTIALS));
+            cq.push_back(make_linear(c->x_act, w.w_cq, w.b_cq, c->qkv, M, D, D, 3 * D, ITB_EPI_BIAS_F32));
+            co.push_back(make_linear(c->ctx, w.w_co, w.b_co, c->y, M, D, D, D, ITB_EPI_BIAS_F32, ITB_Y_PARTIALS));
+            f1.push_back(make_linear(c->x_act, w.w_1, w.b_1, c->ffn_h, M, F, D, F, ITB_EPI_BIAS_GELU_ACT));
+            f2.push_back(make_linear(c->ffn_h, w.w_2, w.b_2, c->y, M, D, F, D, ITB_EPI_BIAS_F32, ITB_Y_PARTIALS));
+            Linear* ls[6] = {&qkv.back(), &o.back(), &cq.back(), &co.back(), &f1.back(), &f2.back()};
+            for (int i = 0; i < 6 && r == 0; ++i) r = ls[i]->prepare(c->dtype, c->gemm_impl);
+        }
+        return r;
+    }
+};
+
+struct itb_decoder {
+    itb_config cfg;
+    LayerSet first, second;              // second: obj_decoder / image pass of the same decoder (cfg.two_stream)
     Linear vocab;
     bool vocab_fused = false;            // 16-bit modes: vocabulary GEMM with the softmax / top-k partials in its epilogue
     CUtensorMap tm_vx, tm_vw, tm_vw2;            // fused launch: activations [M][d] box 128, vocabulary weights [V][d] box 256
@@ -145,23 +167,22 @@ int itb_decoder_create(const itb_config* c, itb_decoder** out) {
     ITB_REQUIRE(c->d % 64 == 0 && c->F % 64 == 0, "decoder_create: hidden and FFN sizes must be multiples of 64");
     ITB_REQUIRE(c->beam >= 1 && c->beam <= 16, "decoder_create: beam width must be in [1,16]");
     ITB_REQUIRE(c->B >= 1 && c->L >= 1 && c->V >= c->beam && c->S >= 1 && c->T_max >= 2, "decoder_create: bad sizes");
+    if (c->two_stream != 0)
+        ITB_REQUIRE(c->layers2_host != nullptr && c->cross_kv2 != nullptr && c->kv_self2 != nullptr && c->stream_gate != nullptr &&
+                    c->x_first != nullptr && c->mem_len2 != nullptr && c->emb2_word != nullptr && c->S2 >= 1,
+                    "decoder_create: two_stream needs layers2 / emb2 / cross_kv2 / kv_self2 / mem_len2 / stream_gate / x_first");
+    if (c->n_prop != 0)
+        ITB_REQUIRE(c->n_prop > 0 && c->proposals != nullptr && c->prop_emb != nullptr && c->lex_gate != nullptr &&
+                    c->lex_ln_g != nullptr && c->lex_ln_b != nullptr, "decoder_create: proposals need prop_emb / lex_gate / lex_ln");
     itb_decoder* d = new itb_decoder();
     d->cfg = *c;
-    d->layers.assign(c->layers_host, c->layers_host + c->L);
-    d->cfg.layers_host = d->layers.data();
-    const int M = c->B * c->beam, D = c->d, F = c->F;
+    const int M = c->B * c->beam, D = c->d;
     const int ldl = (c->V + 3) / 4 * 4;
-    int r = 0;
-    for (int l = 0; l < c->L && r == 0; ++l) {
-        const itb_layer& w = d->layers[l];
-        d->qkv.push_back(make_linear(c->x_act, w.w_qkv, w.b_qkv, c->qkv, M, 3 * D, D, 3 * D, ITB_EPI_BIAS_F32));
-        d->o.push_back(make_linear(c->ctx, w.w_o, w.b_o, c->y, M, D, D, D, ITB_EPI_BIAS_F32, ITB_Y_PARTIALS));
-        d->cq.push_back(make_linear(c->x_act, w.w_cq, w.b_cq, c->qkv, M, D, D, 3 * D, ITB_EPI_BIAS_F32));
-        d->co.push_back(make_linear(c->ctx, w.w_co, w.b_co, c->y, M, D, D, D, ITB_EPI_BIAS_F32, ITB_Y_PARTIALS));
-        d->f1.push_back(make_linear(c->x_act, w.w_1, w.b_1, c->ffn_h, M, F, D, F, ITB_EPI_BIAS_GELU_ACT));
-        d->f2.push_back(make_linear(c->ffn_h, w.w_2, w.b_2, c->y, M, D, F, D, ITB_EPI_BIAS_F32, ITB_Y_PARTIALS));
-        Linear* ls[6] = {&d->qkv.back(), &d->o.back(), &d->cq.back(), &d->co.back(), &d->f1.back(), &d->f2.back()};
-        for (int i = 0; i < 6 && r == 0; ++i) r = ls[i]->prepare(c->dtype, c->gemm_impl);
+    int r = d->first.build(c, c->layers_host);
+    d->cfg.layers_host = d->first.layers.data();
+    if (r == 0 && c->two_stream != 0) {
+        r = d->second.build(c, c->layers2_host);
+        d->cfg.layers2_host = d->second.layers.data();
     }
     if (r == 0 && c->fused_vocab != 0) {
         if (!use_tc(c->dtype, c->gemm_impl) || c->n_chunk != itb_vocab_chunks(c->V)) {
@@ -196,30 +217,56 @@ int itb_decoder_destroy(itb_decoder* dec) {
 
 #define ITB_TRY(x) do { int r_ = (x); if (r_ != 0) return r_; } while (0)
 
+}  // extern "C"
+
+// One pass of a decoder layer stack for the ONE new token of every row: embeddings + LN, then per layer
+// QKV -> self-attention (appends K,V) -> O + LN -> CQ -> cross-attention -> CO + LN -> FFN1 (GELU) -> FFN2 + LN.
+static int run_stack(itb_decoder* dec, const LayerSet& st, const float* emb_word, const float* emb_pos, const float* emb_type,
+                     const float* emb_ln_g, const float* emb_ln_b, void* kv_self, const void* cross_kv,
+                     const unsigned char* src_mask, const int* mem_len, int S, cudaStream_t s) {
+    const itb_config& c = dec->cfg;
+    void* stream = (void*)s;
+    const int M = c.B * c.beam, D = c.d;
+    const size_t esz = (c.dtype == ITB_F32) ? 4 : 2;
+    ITB_TRY(itb_embed_ln(c.dtype, c.ctl, c.tokens, c.tgt_lang, emb_word, emb_pos, emb_type, emb_ln_g, emb_ln_b,
+                         c.ln_eps, c.x_f32, c.x_act, M, c.beam, D, c.T_max, stream));
+    for (int l = 0; l < c.L; ++l) {
+        const itb_layer& w = st.layers[l];
+        char* kv_l = reinterpret_cast<char*>(kv_self) + (size_t)l * M * c.T_max * 2 * D * esz;
+        ITB_TRY(st.qkv[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(itb_self_attention(c.dtype, c.ctl, c.sent_done, c.qkv, kv_l, c.anc, c.ctx, M, c.beam, D, c.H, c.T_max, stream));
+        ITB_TRY(st.o[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, st.o[l].nsplit, w.ln1_g, w.ln1_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
+        ITB_TRY(st.cq[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(itb_cross_attention_impl(c.dtype, c.ctl, c.sent_done, mem_len, c.qkv, 3 * D, cross_kv, l, src_mask, c.ctx, M, c.beam, D,
+                                         c.H, S, c.L, 1, stream));
+        ITB_TRY(st.co[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, st.co[l].nsplit, w.ln2_g, w.ln2_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
+        ITB_TRY(st.f1[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(st.f2[l].run(c.dtype, c.ctl, s));
+        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, st.f2[l].nsplit, w.ln3_g, w.ln3_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
+    }
+    return 0;
+}
+
+extern "C" {
+
 int itb_decoder_step(itb_decoder* dec, void* stream) {
     ITB_REQUIRE(dec != nullptr, "decoder_step: null decoder");
     const itb_config& c = dec->cfg;
     cudaStream_t s = (cudaStream_t)stream;
     const int M = c.B * c.beam, D = c.d;
-    const size_t esz = (c.dtype == ITB_F32) ? 4 : 2;
-    ITB_TRY(itb_embed_ln(c.dtype, c.ctl, c.tokens, c.tgt_lang, c.emb_word, c.emb_pos, c.emb_type, c.emb_ln_g, c.emb_ln_b,
-                         c.ln_eps, c.x_f32, c.x_act, M, c.beam, D, c.T_max, stream));
-    for (int l = 0; l < c.L; ++l) {
-        const itb_layer& w = dec->layers[l];
-        char* kv_l = reinterpret_cast<char*>(c.kv_self) + (size_t)l * M * c.T_max * 2 * D * esz;
-        ITB_TRY(dec->qkv[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(itb_self_attention(c.dtype, c.ctl, c.sent_done, c.qkv, kv_l, c.anc, c.ctx, M, c.beam, D, c.H, c.T_max, stream));
-        ITB_TRY(dec->o[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->o[l].nsplit, w.ln1_g, w.ln1_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
-        ITB_TRY(dec->cq[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(itb_cross_attention_impl(c.dtype, c.ctl, c.sent_done, c.mem_len, c.qkv, 3 * D, c.cross_kv, l, c.src_mask, c.ctx, M, c.beam, D,
-                                         c.H, c.S, c.L, 1, stream));
-        ITB_TRY(dec->co[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->co[l].nsplit, w.ln2_g, w.ln2_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
-        ITB_TRY(dec->f1[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(dec->f2[l].run(c.dtype, c.ctl, s));
-        ITB_TRY(itb_add_ln(c.dtype, c.ctl, c.y, dec->f2[l].nsplit, w.ln3_g, w.ln3_b, c.ln_eps, c.x_f32, c.x_act, M, D, stream));
+    ITB_TRY(run_stack(dec, dec->first, c.emb_word, c.emb_pos, c.emb_type, c.emb_ln_g, c.emb_ln_b, c.kv_self, c.cross_kv, c.src_mask,
+                      c.mem_len, c.S, s));
+    if (c.two_stream != 0) {             // seq_gen.py:167-188
+        ITB_TRY(itb_save_state(c.ctl, c.x_f32, c.x_first, M, D, stream));
+        ITB_TRY(run_stack(dec, dec->second, c.emb2_word, c.emb2_pos, c.emb2_type, c.emb2_ln_g, c.emb2_ln_b, c.kv_self2, c.cross_kv2,
+                          c.src_mask2, c.mem_len2, c.S2, s));
+        ITB_TRY(itb_gate_mix(c.dtype, c.ctl, c.x_first, c.stream_gate, c.gate_eps, c.x_f32, c.x_act, M, D, stream));
     }
+    if (c.n_prop != 0)                   // seq_gen.py:191-192
+        ITB_TRY(itb_attend_proposal(c.dtype, c.ctl, c.proposals, c.n_prop, c.pad_id, c.prop_emb, c.lex_gate, c.lex_ln_g, c.lex_ln_b,
+                                    c.lex_ln_eps, c.x_f32, c.x_act, M, c.beam, D, stream));
     if (dec->vocab_fused)
         ITB_TRY(itb_gemm_tc_vocab(itb_topk_capacity(c.beam), &dec->tm_vx, &dec->tm_vw, &dec->tm_vw2, c.ctl, c.b_vocab, M, c.V, D, c.dtype == ITB_F16 ? 1 : 0,
                                   c.cand_val, c.cand_idx, c.chunk_max, c.chunk_sum, c.logits, (c.V + 3) / 4 * 4, c.n_chunk, s));

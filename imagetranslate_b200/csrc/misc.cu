@@ -146,6 +146,111 @@ __global__ void __launch_bounds__(32 * LN_ROWS, 4) add_ln_kernel(const ItbCtl* _
     ln_row_write<TA>(v, nv, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, lane);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Two-stream decoding (reference src/seq_gen.py:167-188).  The second decoder pass (object-feature stream through
+// `obj_decoder`, or the image memory through the same decoder in the text+image mode) runs on the same buffers as the
+// first; the first stream's last state is parked in x_first meanwhile, and the two are mixed by a learned sigmoid gate:
+//   h = sigmoid(gate + 1e-7) * h_first + (1 - sigmoid(gate + 1e-7)) * h_second
+__global__ void save_state_kernel(const ItbCtl* __restrict__ ctl, const float4* __restrict__ x, float4* __restrict__ dst, int n4) {
+    pdl_trigger();
+    pdl_wait();
+    if (ctl != nullptr && ctl->done) return;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) dst[i] = x[i];
+}
+
+template <typename TA>
+__global__ void gate_mix_kernel(const ItbCtl* __restrict__ ctl, const float* __restrict__ x_first, const float* __restrict__ gate,
+                                float eps_gate, float* __restrict__ x_f32, TA* __restrict__ x_act, int M, int d) {
+    pdl_trigger();
+    pdl_wait();
+    if (ctl != nullptr && ctl->done) return;
+    const int n4 = M * d / 4, d4 = d / 4;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
+        const float4 a = reinterpret_cast<const float4*>(x_first)[i], b = reinterpret_cast<const float4*>(x_f32)[i];
+        const float4 g = reinterpret_cast<const float4*>(gate)[i % d4];
+        const float s0 = 1.f / (1.f + expf(-(g.x + eps_gate))), s1 = 1.f / (1.f + expf(-(g.y + eps_gate)));
+        const float s2 = 1.f / (1.f + expf(-(g.z + eps_gate))), s3 = 1.f / (1.f + expf(-(g.w + eps_gate)));
+        float4 o;
+        o.x = s0 * a.x + (1.f - s0) * b.x;
+        o.y = s1 * a.y + (1.f - s1) * b.y;
+        o.z = s2 * a.z + (1.f - s2) * b.z;
+        o.w = s3 * a.w + (1.f - s3) * b.w;
+        reinterpret_cast<float4*>(x_f32)[i] = o;
+        store4(x_act + (size_t)i * 4, o);
+    }
+}
+
+// Lexical proposals (reference src/seq2seq.py:110-144 `attend_proposal`, called on the last state at src/seq_gen.py:191-192).
+// Per decoder row (sentence b = row / beam): scores_p = h . E[prop[b][p]] (no scaling), probs = softmax_p(scores),
+// ctx = sum_p probs_p E[prop[b][p]]; ctx := 1e-8 when every proposal of the sentence is PAD;
+// h := LayerNorm(sigmoid(lexical_gate + 1e-8) * h + (1 - sigmoid(..)) * ctx).
+// The reference's pad mask `attend_scores[attend_mask].fill_(-10000.0)` (:131) fills a COPY (boolean-mask indexing), so
+// PAD proposals are attended with the PAD row of the embedding table like any other: reproduced, not "fixed".
+#define AP_THREADS 256
+#define AP_MAXP 256
+template <typename TA>
+__global__ void __launch_bounds__(AP_THREADS) attend_proposal_kernel(
+    const ItbCtl* __restrict__ ctl, const int* __restrict__ proposals, int n_prop, int pad, const float* __restrict__ emb,
+    const float* __restrict__ lex_gate, const float* __restrict__ g, const float* __restrict__ b, float eps,
+    float* __restrict__ x_f32, TA* __restrict__ x_act, int beam, int d) {
+    pdl_trigger();
+    pdl_wait();
+    if (ctl != nullptr && ctl->done) return;
+    extern __shared__ float ap_smem[];
+    float* xs = ap_smem;                 // [d]
+    float* sc = ap_smem + d;             // [AP_MAXP]
+    __shared__ float red[32];
+    __shared__ int all_pad;
+    const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int* prop = proposals + (size_t)(r / beam) * n_prop;
+    float* xr = x_f32 + (size_t)r * d;
+    if (tid == 0) all_pad = 1;
+    for (int c = tid; c < d; c += AP_THREADS) xs[c] = xr[c];
+    __syncthreads();
+    for (int p = w; p < n_prop; p += AP_THREADS / 32) {
+        const int id = prop[p];
+        const float* e = emb + (size_t)id * d;
+        float a = 0.f;
+        for (int c = lane; c < d; c += 32) a = fmaf(xs[c], e[c], a);
+        a = warp_sum(a);
+        if (lane == 0) {
+            sc[p] = a;
+            if (id != pad) all_pad = 0;
+        }
+    }
+    __syncthreads();
+    float mx = -3.0e38f;
+    for (int p = 0; p < n_prop; ++p) mx = fmaxf(mx, sc[p]);
+    float den = 0.f;
+    for (int p = 0; p < n_prop; ++p) den += expf(sc[p] - mx);
+    const float inv = 1.f / den;
+    const bool ap = all_pad != 0;
+    // mixed value per column, then LayerNorm (two-pass, fp32)
+    float loc[4];                        // d <= 4 * AP_THREADS
+    float s = 0.f;
+    int k = 0;
+    for (int c = tid; c < d; c += AP_THREADS, ++k) {
+        float ctx = 0.f;
+        if (ap) ctx = 1e-8f;
+        else
+            for (int p = 0; p < n_prop; ++p) ctx = fmaf(expf(sc[p] - mx) * inv, emb[(size_t)prop[p] * d + c], ctx);
+        const float sg = 1.f / (1.f + expf(-(lex_gate[c] + 1e-8f)));
+        loc[k] = sg * xs[c] + (1.f - sg) * ctx;
+        s += loc[k];
+    }
+    const float mean = block_sum(s, red) / (float)d;
+    float q = 0.f;
+    k = 0;
+    for (int c = tid; c < d; c += AP_THREADS, ++k) q += (loc[k] - mean) * (loc[k] - mean);
+    const float rstd = rsqrtf(block_sum(q, red) / (float)d + eps);
+    k = 0;
+    for (int c = tid; c < d; c += AP_THREADS, ++k) {
+        const float o = (loc[k] - mean) * rstd * g[c] + b[c];
+        xr[c] = o;
+        x_act[(size_t)r * d + c] = from_f32<TA>(o);
+    }
+}
+
 // seq_gen.py:109-123: prefix = first token in every slot, scores 0, sizes 0; ancestors = own slot.
 __global__ void init_state_kernel(ItbCtl* ctl, ItbGrp* grp, int* sent_done, const int* __restrict__ sent_grp,
                                   const int* __restrict__ grp_max_len, int G, int* tokens, unsigned char* anc,
@@ -282,6 +387,48 @@ int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, int n_partial, con
         e = itb_launch(add_ln_kernel<float>, lgrid, lblock, smem, s, c, y, n_partial, g, b, eps, x_f32, (float*)x_act, M, d);
     if (e != cudaSuccess) { itb_set_error("add_ln: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("add_ln");
+}
+
+int itb_save_state(const itb_ctl* ctl, const float* x_f32, float* x_first, int M, int d, void* stream) {
+    ITB_REQUIRE(d % 4 == 0 && M > 0, "save_state: d must be a multiple of 4");
+    const int n4 = M * d / 4;
+    cudaError_t e = itb_launch(save_state_kernel, dim3((n4 + 255) / 256 < 1184 ? (n4 + 255) / 256 : 1184), dim3(256), (size_t)0,
+                               (cudaStream_t)stream, reinterpret_cast<const ItbCtl*>(ctl), reinterpret_cast<const float4*>(x_f32),
+                               reinterpret_cast<float4*>(x_first), n4);
+    if (e != cudaSuccess) { itb_set_error("save_state: launch failed: %s", cudaGetErrorString(e)); return -1; }
+    return itb_check_launch("save_state");
+}
+
+int itb_gate_mix(int dtype, const itb_ctl* ctl, const float* x_first, const float* gate, float gate_eps, float* x_f32, void* x_act,
+                 int M, int d, void* stream) {
+    ITB_REQUIRE(d % 4 == 0 && M > 0, "gate_mix: d must be a multiple of 4");
+    const int n4 = M * d / 4;
+    const dim3 grid((n4 + 255) / 256 < 1184 ? (n4 + 255) / 256 : 1184), block(256);
+    cudaStream_t s = (cudaStream_t)stream;
+    const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
+    cudaError_t e;
+    if (dtype == ITB_BF16) e = itb_launch(gate_mix_kernel<__nv_bfloat16>, grid, block, (size_t)0, s, c, x_first, gate, gate_eps, x_f32, (__nv_bfloat16*)x_act, M, d);
+    else if (dtype == ITB_F16) e = itb_launch(gate_mix_kernel<__half>, grid, block, (size_t)0, s, c, x_first, gate, gate_eps, x_f32, (__half*)x_act, M, d);
+    else e = itb_launch(gate_mix_kernel<float>, grid, block, (size_t)0, s, c, x_first, gate, gate_eps, x_f32, (float*)x_act, M, d);
+    if (e != cudaSuccess) { itb_set_error("gate_mix: launch failed: %s", cudaGetErrorString(e)); return -1; }
+    return itb_check_launch("gate_mix");
+}
+
+int itb_attend_proposal(int dtype, const itb_ctl* ctl, const int* proposals, int n_prop, int pad_id, const float* prop_emb,
+                        const float* lex_gate, const float* ln_g, const float* ln_b, float eps, float* x_f32, void* x_act,
+                        int M, int beam, int d, void* stream) {
+    ITB_REQUIRE(n_prop >= 1 && n_prop <= AP_MAXP, "attend_proposal: 1..256 proposals per sentence");
+    ITB_REQUIRE(d <= 4 * AP_THREADS && M > 0 && beam >= 1, "attend_proposal: hidden size above 1024");
+    const dim3 grid(M), block(AP_THREADS);
+    const size_t smem = (size_t)(d + AP_MAXP) * sizeof(float);
+    cudaStream_t s = (cudaStream_t)stream;
+    const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
+    cudaError_t e;
+    if (dtype == ITB_BF16) e = itb_launch(attend_proposal_kernel<__nv_bfloat16>, grid, block, smem, s, c, proposals, n_prop, pad_id, prop_emb, lex_gate, ln_g, ln_b, eps, x_f32, (__nv_bfloat16*)x_act, beam, d);
+    else if (dtype == ITB_F16) e = itb_launch(attend_proposal_kernel<__half>, grid, block, smem, s, c, proposals, n_prop, pad_id, prop_emb, lex_gate, ln_g, ln_b, eps, x_f32, (__half*)x_act, beam, d);
+    else e = itb_launch(attend_proposal_kernel<float>, grid, block, smem, s, c, proposals, n_prop, pad_id, prop_emb, lex_gate, ln_g, ln_b, eps, x_f32, (float*)x_act, beam, d);
+    if (e != cudaSuccess) { itb_set_error("attend_proposal: launch failed: %s", cudaGetErrorString(e)); return -1; }
+    return itb_check_launch("attend_proposal");
 }
 
 int itb_init_state(const itb_config* c, const int* first_tokens, const int* grp_max_len, void* stream) {

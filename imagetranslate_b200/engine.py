@@ -94,8 +94,12 @@ class PackedDecoder(object):
                 setattr(self.layers[i], k, v.data_ptr())
         self.w_ckv = torch.cat(ckv_w, 0).to(device, act).contiguous()          # [L*2d][d]
         self.b_ckv = torch.cat(ckv_b, 0).to(device, torch.float32).contiguous()
-        self.w_vocab, self.b_vocab = mat(output_layer.layer.weight), f32(output_layer.layer.bias)
-        self.V = self.w_vocab.shape[0]
+        if output_layer is not None:
+            self.w_vocab, self.b_vocab = mat(output_layer.layer.weight), f32(output_layer.layer.bias)
+            self.V = self.w_vocab.shape[0]
+        else:                        # second-stream stack (obj_decoder): shares the first stream's vocabulary projection
+            self.w_vocab = self.b_vocab = None
+            self.V = emb.word_embeddings.weight.shape[0]
         self.versions = _src_key(self._src)
 
     def stale(self):
@@ -213,7 +217,7 @@ class DecodeEngine(object):
             self._decoders[key] = dec
         return dec
 
-    def _config(self, pw, B, beam, S, T_max, pad, eos, alpha, G=1, want_logits=False):
+    def _config(self, pw, B, beam, S, T_max, pad, eos, alpha, G=1, want_logits=False, extra=None, S2=0, n_prop=0):
         ws, act, M = self.ws, _ACT[self.dtype_code], B * beam
         V4 = (pw.V + 3) // 4 * 4
         # 16-bit tensor-core decoders: the vocabulary GEMM's epilogue emits the per-chunk max / sum-exp / top-K itself, no
@@ -254,6 +258,29 @@ class DecodeEngine(object):
         t["out_tok"], t["out_len"] = ws.get("out_tok", B * T_max, i32), ws.get("out_len", 2 * B + 8, i32)
         t["first"], t["grp_max_len"] = ws.get("first", B, i32), ws.get("grp_max_len", G, i32)
         t["memory"] = ws.get("memory", B * S * pw.d, act)
+        extra = extra or {}
+        if extra.get("pw2") is not None:          # second decoder stream (reference src/seq_gen.py:167-188)
+            pw2 = extra["pw2"]
+            if (pw2.L, pw2.d, pw2.H, pw2.F) != (pw.L, pw.d, pw.H, pw.F):
+                raise RuntimeError("the second decoder stream must have the first one's shape (layers, hidden, heads, FFN)")
+            c.two_stream, c.S2 = 1, S2
+            c.layers2_host = C.cast(pw2.layers, C.c_void_p)
+            c.emb2_word, c.emb2_pos, c.emb2_type = pw2.emb_word.data_ptr(), pw2.emb_pos.data_ptr(), pw2.emb_type.data_ptr()
+            c.emb2_ln_g, c.emb2_ln_b = pw2.emb_ln_g.data_ptr(), pw2.emb_ln_b.data_ptr()
+            t["memory2"] = ws.get("memory2", B * S2 * pw.d, act)
+            t["cross_kv2"] = ws.get("cross_kv2", B * S2 * pw.L * 2 * pw.d, act)
+            t["kv_self2"] = ws.get("kv_self2", pw.L * M * T_max * 2 * pw.d, act)
+            t["x_first"] = ws.get("x_first", M * pw.d, f32)
+            t["mem_len2"] = ws.get("mem_len2", B, i32)
+            c.cross_kv2, c.kv_self2, c.x_first = t["cross_kv2"].data_ptr(), t["kv_self2"].data_ptr(), t["x_first"].data_ptr()
+            c.mem_len2, c.src_mask2 = t["mem_len2"].data_ptr(), None
+            c.stream_gate, c.gate_eps = extra["gate"].data_ptr(), float(extra.get("gate_eps", 1e-7))
+        if n_prop > 0:                            # lexical proposals (reference src/seq2seq.py:110-144)
+            lex = extra["lex"]
+            t["proposals"] = ws.get("proposals", B * n_prop, i32)
+            c.n_prop, c.proposals = n_prop, t["proposals"].data_ptr()
+            c.prop_emb, c.lex_gate = lex["emb"].data_ptr(), lex["gate"].data_ptr()
+            c.lex_ln_g, c.lex_ln_b, c.lex_ln_eps = lex["ln_g"].data_ptr(), lex["ln_b"].data_ptr(), float(lex["eps"])
         return c, t
 
     @torch.no_grad()
@@ -301,7 +328,7 @@ class DecodeEngine(object):
                                   beam, pad, eos, alpha, trace)[0]
 
     @torch.no_grad()
-    def decode_groups(self, pw, groups, beam, pad, eos, alpha, trace=None):
+    def decode_groups(self, pw, groups, beam, pad, eos, alpha, trace=None, extra=None):
         """Decodes several reference batches ("groups") in lockstep as ONE super-batch: their rows share every kernel
         launch and every weight byte streamed per step, while each group keeps its own loop bound, termination rule and
         memory length, so each group's result is exactly what decoding it alone gives.  groups: list of dicts with the
@@ -316,7 +343,14 @@ class DecodeEngine(object):
         max_len = max(int(g["max_len"]) for g in groups)
         T_max = max(max_len, 2)
         has_mask = any(g["src_mask"] is not None for g in groups)
-        cfg, t = self._config(pw, B, beam, S, T_max, pad, eos, alpha, G, want_logits=trace is not None)
+        extra = extra or {}
+        two = extra.get("pw2") is not None
+        S2s = [int(g["memory2"].shape[1]) for g in groups] if two else []
+        S2 = max(S2s) if two else 0
+        props = [g.get("proposals") for g in groups]
+        n_prop = max(int(p.shape[1]) for p in props) if extra.get("lex") is not None else 0
+        cfg, t = self._config(pw, B, beam, S, T_max, pad, eos, alpha, G, want_logits=trace is not None, extra=extra, S2=S2,
+                              n_prop=n_prop)
         stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         i32 = torch.int32
         cat = lambda k: torch.cat([g[k].to(device=dev, dtype=i32, non_blocking=True).reshape(-1) for g in groups])
@@ -324,10 +358,31 @@ class DecodeEngine(object):
         t["max_lens"][:B].copy_(cat("max_lens"), non_blocking=True)
         t["first"][:B].copy_(cat("first_tokens"), non_blocking=True)
         meta = torch.tensor([gi for gi, n in enumerate(Bs) for _ in range(n)] + [Ss[gi] for gi, n in enumerate(Bs) for _ in range(n)]
-                            + [int(g["max_len"]) for g in groups], dtype=i32).pin_memory().to(dev, non_blocking=True)
+                            + [int(g["max_len"]) for g in groups]
+                            + ([S2s[gi] for gi, n in enumerate(Bs) for _ in range(n)] if two else []),
+                            dtype=i32).pin_memory().to(dev, non_blocking=True)
         t["sent_grp"][:B].copy_(meta[:B], non_blocking=True)
         t["mem_len"][:B].copy_(meta[B:2 * B], non_blocking=True)
-        t["grp_max_len"][:G].copy_(meta[2 * B:], non_blocking=True)
+        t["grp_max_len"][:G].copy_(meta[2 * B:2 * B + G], non_blocking=True)
+        if two:                                   # second memory of every group, zero-padded to the longest
+            t["mem_len2"][:B].copy_(meta[2 * B + G:], non_blocking=True)
+            mem2_all = t["memory2"][:B * S2 * d].view(B, S2, d)
+            if G > 1:
+                mem2_all.zero_()
+            o = 0
+            for g, Bg, Sg in zip(groups, Bs, S2s):
+                mem2_all[o:o + Bg, :Sg].copy_(g["memory2"], non_blocking=True)
+                o += Bg
+            pw2 = extra["pw2"]
+            _lib.check(lib.itb_cross_kv(self.dtype_code, self.gemm_impl, _lib.ptr(mem2_all), _lib.ptr(pw2.w_ckv), _lib.ptr(pw2.b_ckv),
+                                        _lib.ptr(t["cross_kv2"]), B * S2, pw.d, pw.L, stream), "cross_kv2")
+        if n_prop > 0:                            # proposals of every group, PAD-padded to the widest
+            pr_all = t["proposals"][:B * n_prop].view(B, n_prop)
+            pr_all.fill_(pad)
+            o = 0
+            for p_, Bg in zip(props, Bs):
+                pr_all[o:o + Bg, :p_.shape[1]].copy_(p_.to(device=dev, dtype=i32), non_blocking=True)
+                o += Bg
         mem_all = t["memory"][:B * S * d].view(B, S, d)
         mask_all = t["src_mask"][:B * S].view(B, S)
         if G > 1:
@@ -347,7 +402,8 @@ class DecodeEngine(object):
                                     _lib.ptr(t["cross_kv"]), B * S, pw.d, pw.L, stream), "cross_kv")
         _lib.check(lib.itb_init_state(C.byref(cfg), _lib.ptr(t["first"]), _lib.ptr(t["grp_max_len"]), stream), "init_state")
         src_mask = True if has_mask else None
-        key = (pw.uid, B, beam, S, T_max, has_mask, pad, eos, float(alpha), G, trace is not None)
+        key = (pw.uid, B, beam, S, T_max, has_mask, pad, eos, float(alpha), G, trace is not None,
+               extra["pw2"].uid if two else 0, S2, n_prop)
         dec = self._decoder(key, cfg)
         n_steps = max(int(max_len) - 1, 0)
         if trace is None and self.use_graph and n_steps > 0:
@@ -399,7 +455,7 @@ class DecodeEngine(object):
         out_len[2 * B:2 * B + 8].copy_(t["ctl"][:8])
         lens = out_len[:2 * B + 8].cpu()
         self.last_steps = int(lens[2 * B + 2])
-        self.launches_per_step = 2 + 11 * pw.L
+        self.launches_per_step = 2 + 11 * pw.L + ((3 + 11 * pw.L) if two else 0) + (1 if n_prop else 0)
         res, o = [], 0
         for Bg in Bs:
             res.append((tok[o:o + Bg], lens[o:o + Bg], lens[B + o:B + o + Bg]))

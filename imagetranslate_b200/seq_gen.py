@@ -90,6 +90,16 @@ class BeamDecoder(nn.Module):
             self._packed[key] = pw
         return pw
 
+    def _stack_weights(self, key, decoder, code, device):
+        """Packed weights of a decoder stack that has no output layer of its own (obj_decoder: src/image_model.py:279-296)."""
+        key = (key, code, str(device))
+        with self._lock:
+            pw = self._packed.get(key)
+        if pw is None or pw.stale():
+            pw = PackedDecoder(decoder, None, code, device)
+            self._packed[key] = pw
+        return pw
+
     def _enc_weights(self, model, code, device):
         key = ("enc", code, str(device))
         with self._lock:
@@ -135,14 +145,16 @@ class BeamDecoder(nn.Module):
         device = wemb.device
         if device.type != "cuda":
             raise RuntimeError("imagetranslate_b200.BeamDecoder needs the model on a CUDA device (no CPU fallback)")
-        if getattr(model, "use_proposals", False):
-            raise RuntimeError("lexical proposals (attend_proposal) are not supported by the B200 decode path yet")
-        if src_inputs is not None and images is not None:
-            raise RuntimeError("dual text+image stream decoding is not supported by the B200 decode path yet")
+        use_prop = bool(getattr(model, "use_proposals", False))
+        if use_prop and proposals is None:
+            raise RuntimeError("the model uses lexical proposals (use_proposals) but no `proposals` were given")
         batch_lang = int(tgt_langs[0])
+        memory2 = stream2 = None             # second decoder stream (:167-188)
 
+        if images is not None and max_len is None:
+            max_len = 512                                         # :90-91
         with torch.no_grad():
-            if src_inputs is not None:                            # :94-96
+            if src_inputs is not None:                            # :94-96 / :105-106
                 src_mask = src_mask.to(device)
                 code0 = self._dtype_code(wemb)
                 if self.cuda_encoder and self._is_bert_text_encoder(model):
@@ -155,18 +167,26 @@ class BeamDecoder(nn.Module):
                     langs2d = src_langs.unsqueeze(-1).expand(-1, src_inputs.size(-1))
                     memory = model.encode(src_inputs, src_mask, langs2d)[0]
                 mem_mask = src_mask
+                if images is not None:
+                    # :105-106,180-188 text + image: the SAME decoder runs a second pass over the image memory, mixed by
+                    # sigmoid(multimodal_attention_gate).  (As written, the reference's branch cannot run: its encode returns
+                    # the image model's (grid, object) TUPLE as `image_embeddings`, 1-D src_langs, and never repeats the image
+                    # memory per beam -- DESIGN.md §8.  Implemented here as the training forward of the same model defines it:
+                    # src/image_model.py:205-216.)
+                    img = model.image_model(images.to(device).to(wemb.dtype) if wemb.dtype != torch.float32 else images.to(device))
+                    memory2 = img[0] if isinstance(img, (tuple, list)) else img
+                    stream2 = ("same", model.multimodal_attention_gate)
             else:
                 if image_embed is None:                           # :97-99
                     images = images.to(device)
                     if wemb.dtype == torch.float16:
                         images = images.half()
                     memory, obj_feat = model.encode(images=images)
-                    if obj_feat is not None:
-                        raise RuntimeError("object-feature stream (--obj) is not supported by the B200 decode path yet")
+                    if obj_feat is not None:                      # :167-179 object-feature stream through obj_decoder
+                        memory2 = obj_feat
+                        stream2 = ("obj", model.multistream_attention_gate)
                 else:                                             # :100-103
                     memory = image_embed.to(device)
-                if max_len is None and images is not None:
-                    max_len = 512                                 # :90-91
                 mem_mask = None
         B = memory.size(0)
         eos = model.text_processor.sep_token_id()
@@ -185,15 +205,36 @@ class BeamDecoder(nn.Module):
         code = self._dtype_code(wemb)
         return dict(memory=memory, src_mask=mem_mask, first_tokens=first_tokens, tgt_type_ids=tgt_langs, max_lens=max_lens,
                     max_len=max_len, B=B, beam=int(beam_width), pad=int(pad_idx), eos=int(eos), unpad=bool(unpad_output),
-                    lang=batch_lang, code=code, device=device, model=model)
+                    lang=batch_lang, code=code, device=device, model=model, memory2=memory2, stream2=stream2,
+                    proposals=proposals if use_prop else None)
 
     def _decode_groups(self, groups):
         """Runs one super-batch (groups sharing decoder weights / beam / pad / eos) and returns the reference's output
         lists (src/seq_gen.py:229-242), one per group."""
         g0 = groups[0]
-        eng = self._engine(g0["device"], g0["code"])
-        pw = self._weights(g0["model"], g0["lang"], g0["code"], g0["device"])
-        res = eng.decode_groups(pw, groups, g0["beam"], g0["pad"], g0["eos"], float(self.len_penalty_ratio), trace=self.trace)
+        model, code, device = g0["model"], g0["code"], g0["device"]
+        eng = self._engine(device, code)
+        pw = self._weights(model, g0["lang"], code, device)
+        extra = {}
+        kinds = set(None if g["stream2"] is None else g["stream2"][0] for g in groups)
+        if len(kinds) != 1 or len(set(g["proposals"] is None for g in groups)) != 1:
+            raise RuntimeError("batches decoded in lockstep must all use the same decode variant")
+        if g0["stream2"] is not None:
+            kind, gate = g0["stream2"]
+            if kind == "obj":
+                obj_dec = model.obj_decoder[g0["lang"]] if model.lang_dec else model.obj_decoder
+                extra["pw2"] = self._stack_weights(("obj", g0["lang"] if model.lang_dec else -1), obj_dec, code, device)
+            else:
+                extra["pw2"] = pw
+            extra["gate"] = gate.detach().to(device=device, dtype=torch.float32).reshape(-1).contiguous()
+            extra["gate_eps"] = 1e-7                             # :175,185
+        if g0["proposals"] is not None:                          # :191-192 -> src/seq2seq.py:110-144
+            f = lambda t: t.detach().to(device=device, dtype=torch.float32).contiguous()
+            ln = model.lexical_layer_norm
+            extra["lex"] = dict(emb=f(model.proposal_embedding.weight), gate=f(model.lexical_gate).reshape(-1), ln_g=f(ln.weight),
+                                ln_b=f(ln.bias), eps=float(ln.eps))
+        res = eng.decode_groups(pw, groups, g0["beam"], g0["pad"], g0["eos"], float(self.len_penalty_ratio), trace=self.trace,
+                                extra=extra)
         with self._lock:
             self.kernel_launches += eng.last_steps * eng.launches_per_step + 4
         outs = []
@@ -234,7 +275,9 @@ class BeamDecoder(nn.Module):
             beam = kw.get("beam_width") or self.beam_width
             src = self._unwrap(kw.get("src_inputs"))
             S = int(src.size(1)) if src is not None else 49
-            key = (int(tl[0]), beam, kw.get("pad_idx"), src is None, kw.get("max_len"))
+            prop = self._unwrap(kw.get("proposals"))
+            key = (int(tl[0]), beam, kw.get("pad_idx"), src is None, kw.get("max_len"), kw.get("images") is not None,
+                   None if prop is None else int(prop.shape[1]))      # PAD proposals are attended (seq2seq.py:131): no padding
             n = int(first.numel()) * beam
             ok = cur and key == cur_key and cur_rows + n <= rows and max(s_hi, S) <= self.pack_ratio * min(s_lo, S)
             if not ok:

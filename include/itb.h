@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define ITB_ABI_VERSION 3
+#define ITB_ABI_VERSION 4
 #define ITB_Y_PARTIALS 4   /* cfg.y holds up to this many split-K partial outputs: [ITB_Y_PARTIALS][M][d] floats */
 /* dtype codes: (linear-weight type, activation / KV-cache type).  Accumulation, softmax, LayerNorm statistics,
  * logits and beam scores are always fp32. */
@@ -95,6 +95,26 @@ typedef struct {
   float* cand_val; int* cand_idx;           /* [M][n_chunk][KT]                                            */
   float* chunk_max; float* chunk_sum;       /* [M][n_chunk]                                                */
   int* sent_counter;                        /* [B] zero-initialised                                        */
+  /* ---- optional SECOND decoder stream (reference src/seq_gen.py:167-188): the object-feature stream through
+   * `obj_decoder` (:167-179), or the image memory through the SAME decoder in the text+image mode (:180-188).  Each step
+   * runs a second pass of a decoder layer stack over a second memory with its own KV cache (the ancestor table is
+   * shared: same beam); the two last states are mixed by sigmoid(stream_gate + gate_eps) before the vocabulary
+   * projection. ---- */
+  int two_stream, S2;                       /* S2 = second memory length                                   */
+  const itb_layer* layers2_host;            /* HOST array of L entries                                     */
+  const float *emb2_word, *emb2_pos, *emb2_type, *emb2_ln_g, *emb2_ln_b;   /* embeddings of the second stack */
+  const void* cross_kv2;                    /* act [B][S2][L][2][d]                                        */
+  const unsigned char* src_mask2;           /* [B][S2] or NULL                                             */
+  const int* mem_len2;                      /* [B]                                                         */
+  void* kv_self2;                           /* act [L][M][T_max][2][d]                                     */
+  const float* stream_gate;                 /* [d] multistream_attention_gate / multimodal_attention_gate  */
+  float* x_first;                           /* [M][d] scratch: last state of the first stream              */
+  /* ---- optional lexical proposals (reference src/seq2seq.py:110-144, src/seq_gen.py:191-192) ---- */
+  int n_prop, reserved2;                    /* proposals per sentence (0 = off)                            */
+  const int* proposals;                     /* [B][n_prop] token ids                                       */
+  const float* prop_emb;                    /* f32 [V][d]: model.proposal_embedding (= encoder word table) */
+  const float *lex_gate, *lex_ln_g, *lex_ln_b;   /* lexical_gate [d], lexical_layer_norm                   */
+  float lex_ln_eps, gate_eps;               /* gate_eps: 1e-7 (src/seq_gen.py:176,186)                     */
 } itb_config;
 
 typedef struct itb_decoder itb_decoder;
@@ -152,6 +172,19 @@ int itb_self_attention(int dtype, const itb_ctl* ctl, const int* sent_done, cons
 int itb_cross_attention(int dtype, const itb_ctl* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
                         const void* cross_kv, int layer, const unsigned char* src_mask, void* ctx, int M, int beam, int d,
                         int H, int S, int L, void* stream);
+
+/* Two-stream decoding (reference src/seq_gen.py:167-188): x_first := x_f32 (parks the first stream's last state), and
+ * x = sigmoid(gate + gate_eps) * x_first + (1 - sigmoid(gate + gate_eps)) * x, written to x_f32 and its act copy. */
+int itb_save_state(const itb_ctl* ctl, const float* x_f32, float* x_first, int M, int d, void* stream);
+int itb_gate_mix(int dtype, const itb_ctl* ctl, const float* x_first, const float* gate, float gate_eps, float* x_f32,
+                 void* x_act, int M, int d, void* stream);
+
+/* Lexical proposals on the last state (reference src/seq2seq.py:110-144 attend_proposal; src/seq_gen.py:191-192):
+ * x[r] = LayerNorm(sigmoid(lex_gate + 1e-8) * x[r] + (1 - sigmoid(..)) * sum_p softmax_p(x[r] . E[prop[r/beam][p]]) E[..]),
+ * context := 1e-8 for sentences whose proposals are all PAD.  The reference's pad mask is a no-op (it fills a copy); so here. */
+int itb_attend_proposal(int dtype, const itb_ctl* ctl, const int* proposals, int n_prop, int pad_id, const float* prop_emb,
+                        const float* lex_gate, const float* ln_g, const float* ln_b, float eps, float* x_f32, void* x_act,
+                        int M, int beam, int d, void* stream);
 
 /* Fused log-softmax + finished/over-length row zeroing + score add + length-penalty divide + top-k over
  * beam*V + forced-PAD rewrites + back-pointer / prefix / size / score / ancestor-table update + termination

@@ -34,6 +34,14 @@ CASES = {
     # = max_lens[r], and the over-length zeroing / forced PAD (:138-139,197,207) start at that step.
     "text_maxlens_f32": dict(kind="text", V=500, enc=1, dec=1, lang_dec=False, tie=False, B=3, S=180, beam=2, seed=17,
                              eos_bias=-30.0, lens=[180, 90, 170]),
+    # lexical proposals on the last state (src/seq2seq.py:110-144, src/seq_gen.py:191-192): ragged proposal lists padded
+    # with PAD (which the reference attends like any other id), one sentence with only PAD proposals (context := 1e-8)
+    "text_proposals": dict(kind="text", V=700, enc=1, dec=1, lang_dec=False, tie=False, B=4, S=10, beam=3, seed=18,
+                           eos_bias=0.8, proposals=5),
+    # object-feature stream (src/seq_gen.py:167-179): a second decoder (`obj_decoder`, src/image_model.py:279-296) over a
+    # second memory, mixed by sigmoid(multistream_attention_gate); both memories handed over by a patched encode(images=)
+    "image_obj_stream": dict(kind="image_obj", V=650, enc=1, dec=2, lang_dec=False, tie=False, B=3, S=49, S2=7, beam=4, seed=19,
+                             eos_bias=0.0, max_len=12),
 }
 
 GEN = dict(max_len_a=1.3, max_len_b=5, len_penalty_ratio=0.8)   # src/translate.py:26-28 defaults
@@ -59,13 +67,40 @@ def make_text_batch(B, S, V, seed, min_len=4, lens=None):
     return src, mask, pad_idx
 
 
+class _PatchedEncode(object):
+    """Stands in for ImageCaptioning.encode(images=) (src/image_model.py:298-306): hands out fixed (grid memory, object
+    memory) tensors, so that both sides of a parity run decode the same memories."""
+
+    def __init__(self, memory, obj):
+        self.memory, self.obj = memory, obj
+
+    def __call__(self, src_inputs=None, src_mask=None, src_langs=None, images=None):
+        dev = images.device
+        return self.memory.to(dev), self.obj.to(dev)
+
+
+def attach_obj_stream(model, decoder_cls, dec_config, seed):
+    """The attributes BeamDecoder.forward reads for the object stream (src/seq_gen.py:168-177), as
+    ImageCaptioning.__init__ creates them (src/image_model.py:279-296); gate values drawn so that the mix is not 50/50."""
+    torch.manual_seed(seed)
+    model.obj_decoder = decoder_cls(dec_config)
+    model.multistream_attention_gate = torch.nn.Parameter(torch.randn(1, dec_config.hidden_size))
+    return model
+
+
 def build(name):
-    """-> (model, call kwargs for beam_search / BeamDecoder.forward, recipe)"""
+    """-> (model, call kwargs for BeamDecoder.forward, recipe)"""
     c = CASES[name]
     tp = R.FakeTextProcessor(c["V"])
     torch.manual_seed(c["seed"])
     model = R.Seq2SeqModel(tp, lang_dec=c["lang_dec"], tie_embed=c["tie"], enc_layer=c["enc"],
-                           dec_layer=c["dec"]).eval()
+                           dec_layer=c["dec"], use_proposals="proposals" in c)
+    if "proposals" in c:
+        with torch.no_grad():
+            model.lexical_gate.normal_()
+    if c["kind"] == "image_obj":
+        attach_obj_stream(model, R.DecoderModel, model.decoder.config, c["seed"] + 500)
+    model = model.eval()
     B = c["B"]
     tgt = 1
     ol = model.output_layer if ((not c["lang_dec"]) and c["tie"]) else model.output_layer[tgt]
@@ -78,10 +113,37 @@ def build(name):
         kw.update(src_inputs=src, src_mask=mask, src_sizes=pad_idx, src_langs=torch.zeros(B, dtype=torch.long))
         if "max_len" in c:
             kw.update(max_len=c["max_len"])
+        if "proposals" in c:
+            g = torch.Generator().manual_seed(c["seed"] + 3000)
+            prop = torch.randint(7, c["V"], (B, c["proposals"]), generator=g)
+            prop[1, 3:] = 0
+            prop[2, :] = 0                                     # only PAD proposals
+            prop[3, 1:] = 0
+            kw.update(proposals=prop)
     else:
         g = torch.Generator().manual_seed(c["seed"] + 2000)
-        kw.update(image_embed=torch.randn(B, c["S"], 768, generator=g), max_len=c["max_len"])
+        mem = torch.randn(B, c["S"], 768, generator=g)
+        if c["kind"] == "image":
+            kw.update(image_embed=mem, max_len=c["max_len"])
+        else:
+            obj = torch.randn(B, c["S2"], 768, generator=g)
+            obj[1, 4:] = 0                                     # images with fewer objects: zero rows, still attended (no mask)
+            obj[2, 2:] = 0
+            model.encode = _PatchedEncode(mem, obj)
+            kw.update(images=torch.zeros(B, 1), max_len=c["max_len"])
     return model, kw, c
+
+
+def run_oracle(model, kw, **opts):
+    """The restated oracle on the keyword arguments of BeamDecoder.forward (maps a patched encode(images=) to the two
+    memories of the object stream)."""
+    kw = dict(kw)
+    if "images" in kw:
+        mem, obj = model.encode(images=kw.pop("images"))
+        kw["image_embed"] = mem
+        if obj is not None:
+            opts.update(memory2=obj, decoder2=model.obj_decoder, gate=model.multistream_attention_gate)
+    return R.beam_search(model, **GEN, **kw, **opts)
 
 
 def weights_digest(model):

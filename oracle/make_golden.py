@@ -48,7 +48,11 @@ def run_reference(name, record=False):
     ns = reference_loader.load()
     model, kw, c = cases.build(name)
     ref = ns.mass_seq2seq.MassSeq2Seq(model.text_processor, lang_dec=c["lang_dec"], tie_embed=c["tie"],
-                                      enc_layer=c["enc"], dec_layer=c["dec"]).eval()
+                                      enc_layer=c["enc"], dec_layer=c["dec"], use_proposals="proposals" in c)
+    if c["kind"] == "image_obj":
+        cases.attach_obj_stream(ref, ns.bert_seq2seq.BertDecoderModel, ref.decoder.config, c["seed"] + 500)
+        ref.encode = model.encode                 # the same fixed (grid, object) memories on both sides
+    ref = ref.eval()
     missing = ref.load_state_dict(model.state_dict())
     assert not missing.missing_keys and not missing.unexpected_keys
     kw = dict(kw)

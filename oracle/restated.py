@@ -126,7 +126,6 @@ class Seq2SeqModel(nn.Module):
     def __init__(self, text_processor, lang_dec=True, use_proposals=False, tie_embed=False, enc_layer=6,
                  dec_layer=3, embed_dim=768, intermediate_dim=3072):
         super().__init__()
-        assert not use_proposals, "attend_proposal is a 'next' row (SURVEY §8f-3)"
         self.text_processor = text_processor
         n_lang = len(text_processor.languages)
         self.config = bert_config(text_processor.tokenizer.get_vocab_size(), n_lang, enc_layer, embed_dim,
@@ -168,10 +167,32 @@ class Seq2SeqModel(nn.Module):
                 dec._tie_or_clone_weights(self.encoder.embeddings.token_type_embeddings,
                                           dec.embeddings.token_type_embeddings)
 
+        if use_proposals:  # src/seq2seq.py:79-83
+            self.proposal_embedding = self.encoder.embeddings.word_embeddings
+            self.lexical_gate = nn.Parameter(torch.zeros(1, self.config.hidden_size).fill_(0.1), requires_grad=True)
+            self.lexical_layer_norm = nn.LayerNorm(self.config.hidden_size, eps=self.config.layer_norm_eps)
+
     def encode(self, src_inputs, src_mask, src_langs, images=None):
         dev = self.encoder.embeddings.word_embeddings.weight.device
         return (self.encoder(src_inputs.to(dev), attention_mask=src_mask.to(dev),
                              token_type_ids=src_langs.to(dev)), None)
+
+    def attend_proposal(self, decoder_output, proposals, pad_idx):
+        """src/seq2seq.py:110-144 for the 2-D (last state) input of the decode path (:126-131 branch).  Line 136,
+        `attend_scores[attend_mask].fill_(-10000.0)`, fills a COPY (boolean-mask indexing): PAD proposals stay attended."""
+        dev = self.encoder.embeddings.word_embeddings.weight.device
+        proposals = proposals.to(dev)
+        emb = self.proposal_embedding(proposals)                              # (B,P,d)
+        if len(proposals) < len(decoder_output):
+            beam = int(len(decoder_output) / len(proposals))
+            proposals = torch.repeat_interleave(proposals, beam, 0)
+            emb = torch.repeat_interleave(emb, beam, 0)
+        scores = torch.matmul(decoder_output.unsqueeze(1), emb.transpose(-1, -2)).squeeze(-2)   # (M,P), unscaled, unmasked
+        probs = torch.softmax(scores, dim=-1)
+        ctx = torch.sum(probs.unsqueeze(-1) * emb, dim=-2)
+        ctx[torch.all(proposals == pad_idx, dim=-1)] = 1e-8
+        sig = torch.sigmoid(self.lexical_gate + 1e-8)
+        return self.lexical_layer_norm(sig * decoder_output + (1 - sig) * ctx)
 
 
 def len_penalty(lengths, alpha):
@@ -259,8 +280,11 @@ def lowest_index_topk(cand, k):
 def beam_search(model, src_inputs=None, src_sizes=None, first_tokens=None, src_mask=None, src_langs=None,
                 tgt_langs=None, pad_idx=None, max_len=None, unpad_output=True, beam_width=5, image_embed=None,
                 max_len_a=1.1, max_len_b=5, len_penalty_ratio=0.8, trace=None, topk_fn=None,
-                teacher_prefixes=None):
+                teacher_prefixes=None, proposals=None, memory2=None, decoder2=None, gate=None):
     """src/seq_gen.py:46-242 for the text (`src_inputs`) and `image_embed` memories.
+
+    Second decoder stream (:167-188): `memory2` (B,S2,d) is decoded by `decoder2` (obj_decoder; or the model's own decoder
+    for the text+image mode) with no memory mask, and mixed by sigmoid(gate + 1e-7).  `proposals` (B,P): :191-192.
 
     trace: optional list; per step a dict(i, last_state, log_probs, prefixes, scores, sizes, raw_idx)
     is appended (the recorder of SURVEY Appendix D.6).
@@ -300,7 +324,14 @@ def beam_search(model, src_inputs=None, src_sizes=None, first_tokens=None, src_m
         mmask = rep(src_mask) if src_inputs is not None else None
         states = decoder(encoder_states=mem, input_ids=cur, encoder_attention_mask=mmask,
                          tgt_attention_mask=torch.ones(cur.size(), device=device), token_type_ids=types)
+        if memory2 is not None:                                           # :167-188
+            st2 = decoder2(encoder_states=rep(memory2.to(device)), input_ids=cur, encoder_attention_mask=None,
+                           tgt_attention_mask=torch.ones(cur.size(), device=device), token_type_ids=types)
+            sig = torch.sigmoid(gate + 1e-7)
+            states = sig * states + (1 - sig) * st2
         last = states[:, -1, :]                                           # :190
+        if model.use_proposals:                                           # :191-192
+            last = model.attend_proposal(last, proposals, pad_idx)
         logp = F.log_softmax(out_layer(last), dim=-1)                     # :194
         prefixes, scores, sizes, raw_idx = search_step(i, logp, prefixes, scores, sizes, max_lens, eos, pad_idx,
                                                        beam, len_penalty_ratio, topk_fn)

@@ -22,11 +22,11 @@ def test_restated_oracle_matches_reference_fixture(name):
     tokens, lengths, full, meta = load_golden(name)
     model, kw, c = cases.build(name)
     assert cases.weights_digest(model) == meta["weights_sha256"], "seeded weights differ from the fixture's"
-    outs = R.beam_search(model, **cases.GEN, **kw)
+    outs = cases.run_oracle(model, kw)
     assert [len(o) for o in outs] == lengths.tolist()
     for r, o in enumerate(outs):
         assert o.tolist() == tokens[r, :lengths[r]].tolist()
-    outs_full = R.beam_search(model, unpad_output=False, **cases.GEN, **kw)
+    outs_full = cases.run_oracle(model, kw, unpad_output=False)
     assert torch.stack(outs_full).numpy().tolist() == full.tolist()
 
 
