@@ -21,6 +21,35 @@ def available():
     return os.path.isfile(os.path.join(REF_SRC, "seq_gen.py"))
 
 
+def _patch_text_processor(ns):
+    """tokenizers 0.22 cannot `save(directory)` (src/textprocessor.py:43) nor re-read a merges.txt holding a newline merge:
+    the oracle's TextProcessor serialises tokenizer.json instead (SURVEY §8c blocker 4, Appendix D.5).  Tokenisation is
+    outside the hot path; both sides of a parity run consume the same ids."""
+    import os as _os
+    import pickle
+    import tokenizers
+    base = ns.textprocessor.TextProcessor
+
+    class TextProcessor(base):
+        def __init__(self, tok_model_path=None):
+            self.languages = {}
+            if tok_model_path is not None:
+                self.tokenizer = tokenizers.Tokenizer.from_file(_os.path.join(tok_model_path, "tokenizer.json"))
+                with open(_os.path.join(tok_model_path, "langs"), "rb") as fp:
+                    self.languages = pickle.load(fp)
+            self.init_properties(self.languages)
+
+        def save(self, directory):
+            _os.makedirs(directory, exist_ok=True)
+            self.tokenizer.save(_os.path.join(directory, "tokenizer.json"))
+            with open(_os.path.join(directory, "langs"), "wb") as fp:
+                pickle.dump(self.languages, fp)
+
+    ns.textprocessor.TextProcessor = TextProcessor
+    ns.seq2seq.TextProcessor = TextProcessor
+    ns.TextProcessor = TextProcessor
+
+
 def load():
     """Returns a namespace with the reference modules: seq_gen, seq2seq, mass_seq2seq, bert_seq2seq."""
     if "ns" in _cache:
@@ -38,8 +67,9 @@ def load():
         apex.amp.initialize = lambda m, **kw: m
         sys.modules["apex"] = apex
         sys.modules["apex.amp"] = apex.amp
+        import torch
         frc = types.ModuleType("faster_rcnn_feats")
-        frc.fasterrcnn_resnet50_fpn = lambda *a, **k: None
+        frc.fasterrcnn_resnet50_fpn = lambda *a, **k: torch.nn.Identity()       # callable returning a dummy module (D.3)
         sys.modules["faster_rcnn_feats"] = frc
 
         src = open(os.path.join(REF_SRC, "seq_gen.py")).read()
@@ -65,7 +95,20 @@ def load():
         exec(compile(rec_src, seq_gen.__file__, "exec"), seq_gen_rec.__dict__)
 
         ns = types.SimpleNamespace(seq_gen=seq_gen, seq_gen_rec=seq_gen_rec)
-        for name in ("bert_seq2seq", "seq2seq", "mass_seq2seq", "dataset"):
+        for name in ("bert_seq2seq", "seq2seq", "mass_seq2seq", "dataset", "textprocessor"):
+            setattr(ns, name, importlib.import_module(name))
+        _patch_text_processor(ns)
+        # image_model.init_net asks torchvision for pretrained weights (src/image_model.py:87-97): no network here, so the
+        # torchvision constructors are wrapped to build the same architectures with random init
+        import torchvision.models as tvm
+        for fn in ("resnet18", "resnet34", "resnet50", "resnet101", "resnet152", "resnext101_32x8d"):
+            orig = getattr(tvm, fn)
+            if not getattr(orig, "_itb_wrapped", False):
+                def wrapped(pretrained=False, _orig=orig, **kw):
+                    return _orig(weights=None, **kw)
+                wrapped._itb_wrapped = True
+                setattr(tvm, fn, wrapped)
+        for name in ("image_model", "translate", "caption"):
             setattr(ns, name, importlib.import_module(name))
     finally:
         sys.path.remove(SHIM)
