@@ -68,6 +68,7 @@ _SIGS = {
     "itb_save_state": (C.c_int, [P, P, P, C.c_int, C.c_int, P]),
     "itb_gate_mix": (C.c_int, [C.c_int, P, P, P, C.c_float, P, P, C.c_int, C.c_int, P]),
     "itb_attend_proposal": (C.c_int, [C.c_int, P, P, C.c_int, C.c_int, P, P, P, P, C.c_float, P, P, C.c_int, C.c_int, C.c_int, P]),
+    "itb_kv_gather": (C.c_int, [C.c_int, P, P, P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, P]),
     "itb_beam_step": (C.c_int, [C.POINTER(Config), P]),
     "itb_finalize": (C.c_int, [P, P, P, P, P, C.c_int, P, P, P, C.c_int, C.c_int, C.c_int, P]),
     "itb_init_state": (C.c_int, [C.POINTER(Config), P, P, P]),

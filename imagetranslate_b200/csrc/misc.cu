@@ -251,6 +251,18 @@ __global__ void __launch_bounds__(AP_THREADS) attend_proposal_kernel(
     }
 }
 
+// Physical reorder of the self-attention KV cache by back-pointer: dst[l][r][p] = src[l][src_row[r]][p] for p < n_pos.
+// This is what a direct translation of the reference's `top_beam_outputs.gather(1, beam_indices)` (src/seq_gen.py:217-219)
+// implies for a KV cache.  The decode path does NOT use it -- the ancestor table replaces it -- it exists so that the two
+// variants can be measured against each other (tools/kv_reorder_bench.py, profiles/).
+__global__ void kv_gather_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, const int* __restrict__ src_row,
+                                 int M, size_t row_units, int n_units) {
+    const int r = blockIdx.x, l = blockIdx.y;
+    const uint4* s = src + ((size_t)l * M + src_row[r]) * row_units;
+    uint4* d = dst + ((size_t)l * M + r) * row_units;
+    for (int i = threadIdx.x; i < n_units; i += blockDim.x) d[i] = s[i];
+}
+
 // seq_gen.py:109-123: prefix = first token in every slot, scores 0, sizes 0; ancestors = own slot.
 __global__ void init_state_kernel(ItbCtl* ctl, ItbGrp* grp, int* sent_done, const int* __restrict__ sent_grp,
                                   const int* __restrict__ grp_max_len, int G, int* tokens, unsigned char* anc,
@@ -429,6 +441,18 @@ int itb_attend_proposal(int dtype, const itb_ctl* ctl, const int* proposals, int
     else e = itb_launch(attend_proposal_kernel<float>, grid, block, smem, s, c, proposals, n_prop, pad_id, prop_emb, lex_gate, ln_g, ln_b, eps, x_f32, (float*)x_act, beam, d);
     if (e != cudaSuccess) { itb_set_error("attend_proposal: launch failed: %s", cudaGetErrorString(e)); return -1; }
     return itb_check_launch("attend_proposal");
+}
+
+int itb_kv_gather(int dtype, const void* kv_src, void* kv_dst, const int* src_row, int M, int T_max, int n_pos, int d, int L,
+                  void* stream) {
+    ITB_REQUIRE(M > 0 && L > 0 && n_pos >= 0 && n_pos <= T_max && d % 8 == 0, "kv_gather: bad sizes");
+    const size_t esz = dtype == ITB_F32 ? 4 : 2;
+    const size_t row_units = (size_t)T_max * 2 * d * esz / 16;
+    const int n_units = (int)((size_t)n_pos * 2 * d * esz / 16);
+    if (n_units == 0) return 0;
+    kv_gather_kernel<<<dim3(M, L), 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const uint4*>(kv_src), reinterpret_cast<uint4*>(kv_dst),
+                                                                    src_row, M, row_units, n_units);
+    return itb_check_launch("kv_gather");
 }
 
 int itb_init_state(const itb_config* c, const int* first_tokens, const int* grp_max_len, void* stream) {

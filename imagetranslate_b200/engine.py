@@ -165,7 +165,9 @@ class Workspace(object):
     def get(self, name, numel, dtype):
         t = self.buf.get(name)
         if t is None or t.numel() < numel or t.dtype != dtype:
-            t = torch.empty(max(int(numel), 1), dtype=dtype, device=self.device)
+            # grow geometrically: every growth invalidates the cached decoders (raw pointers), so it has to be rare
+            grown = int(numel) if t is None or t.dtype != dtype else max(int(numel), int(t.numel() * 1.5))
+            t = torch.empty(max(grown, 1), dtype=dtype, device=self.device)
             self.buf[name] = t
             self.generation += 1
         return t
@@ -173,7 +175,10 @@ class Workspace(object):
 
 class DecodeEngine(object):
     GRAPH_STEPS = 8          # search steps per CUDA-graph replay
-    MAX_CACHED = 48          # decoders (TMA descriptors + instantiated graph) kept per engine
+    MAX_CACHED = 256         # decoders (TMA descriptors + instantiated graph) kept per engine, least recently used first out
+    S_QUANTUM, T_QUANTUM = 8, 16     # memory length / cache capacity are rounded up to these, so that a corpus of ragged
+                                     # batches maps onto a small lattice of decoder shapes (the real lengths travel as data:
+                                     # mem_len per sentence, loop bound per group)
 
     def __init__(self, device, dtype_code, gemm_impl=_lib.GEMM_AUTO, poll_every=16, use_graph=True):
         self.device = torch.device(device)
@@ -188,6 +193,7 @@ class DecodeEngine(object):
         self.last_steps = 0
         self.launches_per_step = None
         self._decoders = {}          # shape key -> itb_decoder* (C.c_void_p)
+        self.decoders_created = 0
         self._dec_generation = -1
         self._ctl_host = [torch.empty(8, dtype=torch.int32).pin_memory() for _ in range(4)]
 
@@ -208,13 +214,14 @@ class DecodeEngine(object):
         if self._dec_generation != self.ws.generation:       # some workspace buffer moved: every cached pointer is stale
             self._drop_decoders()
             self._dec_generation = self.ws.generation
-        dec = self._decoders.get(key)
+        dec = self._decoders.pop(key, None)
         if dec is None:
             if len(self._decoders) >= self.MAX_CACHED:
                 self.lib.itb_decoder_destroy(self._decoders.pop(next(iter(self._decoders))))
             dec = C.c_void_p()
             _lib.check(self.lib.itb_decoder_create(C.byref(cfg), C.byref(dec)), "decoder_create")
-            self._decoders[key] = dec
+            self.decoders_created += 1
+        self._decoders[key] = dec           # (re-)inserted last: dict order = recency
         return dec
 
     def _config(self, pw, B, beam, S, T_max, pad, eos, alpha, G=1, want_logits=False, extra=None, S2=0, n_prop=0):
@@ -337,16 +344,17 @@ class DecodeEngine(object):
         G = len(groups)
         Bs = [int(g["memory"].shape[0]) for g in groups]
         Ss = [int(g["memory"].shape[1]) for g in groups]
-        B, S, d = sum(Bs), max(Ss), int(groups[0]["memory"].shape[2])
+        q = lambda v, m: -(-int(v) // m) * m
+        B, S, d = sum(Bs), q(max(Ss), self.S_QUANTUM), int(groups[0]["memory"].shape[2])
         if d != pw.d:
             raise RuntimeError("memory width %d does not match the decoder width %d" % (d, pw.d))
         max_len = max(int(g["max_len"]) for g in groups)
-        T_max = max(max_len, 2)
+        T_max = q(max(max_len, 2), self.T_QUANTUM)
         has_mask = any(g["src_mask"] is not None for g in groups)
         extra = extra or {}
         two = extra.get("pw2") is not None
         S2s = [int(g["memory2"].shape[1]) for g in groups] if two else []
-        S2 = max(S2s) if two else 0
+        S2 = q(max(S2s), self.S_QUANTUM) if two else 0
         props = [g.get("proposals") for g in groups]
         n_prop = max(int(p.shape[1]) for p in props) if extra.get("lex") is not None else 0
         cfg, t = self._config(pw, B, beam, S, T_max, pad, eos, alpha, G, want_logits=trace is not None, extra=extra, S2=S2,
@@ -367,7 +375,7 @@ class DecodeEngine(object):
         if two:                                   # second memory of every group, zero-padded to the longest
             t["mem_len2"][:B].copy_(meta[2 * B + G:], non_blocking=True)
             mem2_all = t["memory2"][:B * S2 * d].view(B, S2, d)
-            if G > 1:
+            if any(Sg != S2 for Sg in S2s):
                 mem2_all.zero_()
             o = 0
             for g, Bg, Sg in zip(groups, Bs, S2s):
@@ -385,7 +393,7 @@ class DecodeEngine(object):
                 o += Bg
         mem_all = t["memory"][:B * S * d].view(B, S, d)
         mask_all = t["src_mask"][:B * S].view(B, S)
-        if G > 1:
+        if any(Sg != S for Sg in Ss):       # padded positions are never attended (mem_len), but their K,V must be finite
             mem_all.zero_()
         o = 0
         for g, Bg, Sg in zip(groups, Bs, Ss):

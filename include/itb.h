@@ -186,6 +186,13 @@ int itb_attend_proposal(int dtype, const itb_ctl* ctl, const int* proposals, int
                         const float* lex_gate, const float* ln_g, const float* ln_b, float eps, float* x_f32, void* x_act,
                         int M, int beam, int d, void* stream);
 
+/* Physical KV-cache reorder by back-pointer: kv_dst[l][r][p] = kv_src[l][src_row[r]][p], p < n_pos, caches [L][M][T_max][2][d].
+ * What a literal KV-cached port of reference src/seq_gen.py:217-219 (gather of the prefixes by beam index) would run every
+ * step.  NOT on the decode path (the ancestor table in itb_beam_step / itb_self_attention replaces it); exported so the two
+ * variants can be measured side by side. */
+int itb_kv_gather(int dtype, const void* kv_src, void* kv_dst, const int* src_row, int M, int T_max, int n_pos, int d, int L,
+                  void* stream);
+
 /* Fused log-softmax + finished/over-length row zeroing + score add + length-penalty divide + top-k over
  * beam*V + forced-PAD rewrites + back-pointer / prefix / size / score / ancestor-table update + termination
  * bookkeeping.  Replaces reference src/seq_gen.py:134-143 and :194-227. */

@@ -266,3 +266,25 @@ def test_full_size_superbatch_agrees_with_per_batch_decode(dtype, floor):
     # bf16 rounding and one flipped near-tie changes the rest of the sentence; fp16's 8x finer rounding
     # shows that the large builds themselves are accurate.  A broken large-launch kernel gives ~0.
     assert total == 1024 and same >= floor * total
+
+
+@pytest.mark.parametrize("beam", [1, 4, 12])
+def test_fp32_long_source_256_tokens_matches_oracle(beam):
+    """BASELINE.json configs[3] shape: sources of 256 tokens, T = 337 steps, beam 1 (no length penalty, src/seq_gen.py:200-201)
+    / 4 / 12 -- long ancestor tables, many attention stages, contexts beyond the 32 positions kept in registers.  The oracle
+    (full-prefix recompute over up to 337 positions) runs on the GPU in fp32 to finish in seconds."""
+    V, B, S = 2000, 3, 256
+    tp = R.FakeTextProcessor(V)
+    torch.manual_seed(97)
+    model = R.Seq2SeqModel(tp, lang_dec=False, tie_embed=False, enc_layer=1, dec_layer=1).eval()
+    with torch.no_grad():
+        model.output_layer[1].layer.bias[4] -= 2.0                    # EOS is rare: most rows run the full 337 steps
+    src, mask, pad_idx = cases.make_text_batch(B, S, V, 98, min_len=200)
+    kw = dict(src_inputs=src, src_mask=mask, src_sizes=pad_idx, src_langs=torch.zeros(B, dtype=torch.long),
+              first_tokens=torch.full((B,), 6), tgt_langs=torch.ones(B, dtype=torch.long), pad_idx=0)
+    model = model.to(DEV)
+    assert not torch.backends.cuda.matmul.allow_tf32
+    want = R.beam_search(model, beam_width=beam, **cases.GEN, **{k: (v.to(DEV) if torch.is_tensor(v) else v) for k, v in kw.items()})
+    got, _ = _decode(model, dict(kw, beam_width=beam), "fp32")
+    assert max(len(w) for w in want) > 250
+    assert [g.tolist() for g in got] == [w.tolist() for w in want]
