@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--no-extras", action="store_true", help="skip the per-batch / GPU-eager / extra roofline legs")
     ap.add_argument("--cpu-sentences", type=int, default=16)
     ap.add_argument("--cpu-full", action="store_true", help="cpu baseline on the FULL median batch (minutes)")
+    ap.add_argument("--no-gather", action="store_true", help="diagnostic: leave the NCCL output gather out of the passes (N > 1)")
     return ap.parse_args()
 
 
@@ -381,7 +382,7 @@ def run_text(args, rank, world, local_rank):
                 outs += o
         n_launch = gen.kernel_launches - n0
         toks = emitted(outs)
-        if world > 1:                                  # the NCCL output gather is part of every pass at N > 1
+        if world > 1 and not args.no_gather:           # the NCCL output gather is part of every pass at N > 1
             res = gather_outputs(ids, outs, dev)
             if rank == 0:
                 gathered["n"] = len(res)
@@ -391,7 +392,7 @@ def run_text(args, rank, world, local_rank):
     sampler = ClockSampler(local_rank) if rank == 0 else None
     ms, toks, launches, clocks = _timed(lambda: one_pass(dev_kw), args.steps, args.warmup, dev, world, sampler)
     ms_e, toks_e, _, _ = _timed(lambda: one_pass(host_kw), args.steps, 1, dev, world)
-    if world > 1 and rank == 0:
+    if world > 1 and rank == 0 and not args.no_gather:
         assert gathered["n"] == n_total, "gather returned %d of %d sentences" % (gathered["n"], n_total)
         assert gathered["tokens"] * args.steps == int(toks_e), "gathered token count differs from the ranks' own"
     d2h = int(toks_e / max(args.steps, 1) / world) * 4

@@ -21,6 +21,7 @@
 // CUDA-core formulation, which was issue-bound at ~17 % of HBM bandwidth (profiles/r1_attn_*.txt).
 #include "common.cuh"
 #include "launch.h"
+#include "mma16.cuh"
 
 #define DH 64
 #define AM_WARPS 4
@@ -45,40 +46,6 @@ struct AttnMmaArgs {
     void* ctx;                           // act [M][d]
     int M, beam, d, T_max, S, L, layer, n_warps;
 };
-
-template <typename T> struct Mma16;
-template <> struct Mma16<__nv_bfloat16> {
-    static __device__ __forceinline__ void mma(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
-        asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                     : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-                     : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-    }
-    static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
-        __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
-        return *reinterpret_cast<uint32_t*>(&h);
-    }
-    static __device__ __forceinline__ float2 unpack(uint32_t u) { return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u)); }
-};
-template <> struct Mma16<__half> {
-    static __device__ __forceinline__ void mma(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
-        asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                     : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-                     : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-    }
-    static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
-        __half2 h = __floats2half2_rn(lo, hi);
-        return *reinterpret_cast<uint32_t*>(&h);
-    }
-    static __device__ __forceinline__ float2 unpack(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
-};
-
-// hi/lo split of a pair of fp32 values into two packed 16-bit registers: x = hi + lo up to ~2^-17 relative.
-template <typename T>
-__device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t& lo) {
-    hi = Mma16<T>::pack(x, y);
-    const float2 h = Mma16<T>::unpack(hi);
-    lo = Mma16<T>::pack(x - h.x, y - h.y);
-}
 
 template <typename T, bool SELF, int STAGE>
 __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(AttnMmaArgs a) {
@@ -440,10 +407,18 @@ static int launch_attn_mma(AttnMmaArgs a, bool self, cudaStream_t s) {
     return small_stage ? launch_attn_mma_stage<T, 32>(a, self, s) : launch_attn_mma_stage<T, 64>(a, self, s);
 }
 
-// Called by itb_self_attention / itb_cross_attention (attention.cu) for the 16-bit dtypes.
+bool itb_attn_bulk_applies(bool self, int M, int beam, int d, int T_max, int S);
+int itb_attn_bulk(int dtype, bool self, const void* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
+                  void* kv, const unsigned char* anc, const unsigned char* mask, void* ctx, int M, int beam, int d, int T_max,
+                  int S, int L, int layer, cudaStream_t s);
+
+// Called by itb_self_attention / itb_cross_attention (attention.cu) for the 16-bit dtypes.  Large launches go to the
+// bulk-copy producer / consumer kernel (attention_bulk.cu), small ones stay on the warp-per-head kernel above.
 int itb_attn_mma(int dtype, bool self, const void* ctl, const int* sent_done, const int* mem_len, const float* q, int ldq,
                  void* kv, const unsigned char* anc, const unsigned char* mask, void* ctx, int M, int beam, int d, int T_max,
                  int S, int L, int layer, int early_kv, cudaStream_t s) {
+    if (itb_attn_bulk_applies(self, M, beam, d, T_max, S))
+        return itb_attn_bulk(dtype, self, ctl, sent_done, mem_len, q, ldq, kv, anc, mask, ctx, M, beam, d, T_max, S, L, layer, s);
     AttnMmaArgs a = {};
     a.early_kv = early_kv;
     a.ctl = reinterpret_cast<const ItbCtl*>(ctl);

@@ -2,7 +2,9 @@
 in a child process (the switches are read once per process) so the small parity cases cover them too:
  * ITB_ATTN_STAGE=32 -- the 32-position / 4-CTAs-per-SM build of the tensor-core attention kernel, which the library
    only selects for launches of more than ~2 waves (4096 beam rows); ITB_ATTN_STAGE=64 is the small-launch build;
- * ITB_VOCAB_PAIR=1 -- the CTA-pair (tcgen05 cta_group::2) launch of the fused vocabulary projection."""
+ * ITB_VOCAB_PAIR=1 -- the CTA-pair (tcgen05 cta_group::2) launch of the fused vocabulary projection;
+ * ITB_ATTN_BULK=1 / 0 -- the bulk-copy producer / consumer attention kernel (csrc/attention_bulk.cu), which the library
+   selects for launches of >= 96 work items (sentences x beam groups), forced on for every 16-bit attention launch / off."""
 import os
 import subprocess
 import sys
@@ -33,3 +35,21 @@ def test_decode_parity_with_the_many_wave_attention_build():
 
 def test_fused_vocab_projection_on_cta_pairs():
     _run({"ITB_VOCAB_PAIR": "1"}, "fused_vocab")
+
+
+def test_attention_kernels_on_the_bulk_copy_kernel():
+    _run({"ITB_ATTN_BULK": "1"}, "attention")
+
+
+def test_decode_parity_on_the_bulk_copy_attention_kernel():
+    _run({"ITB_ATTN_BULK": "1"}, "16bit or forward_many or encoder", path="tests/test_gpu_decode.py")
+    _run({"ITB_ATTN_BULK": "1"}, "whole_vocabulary or free_running", path="tests/test_gpu_parity16.py")
+
+
+def test_decode_variants_on_the_bulk_copy_attention_kernel():
+    _run({"ITB_ATTN_BULK": "1"}, "text_plus_image", path="tests/test_gpu_decode_variants.py")
+
+
+def test_full_size_superbatch_without_the_bulk_copy_kernel():
+    """the warp-per-head kernel at the full launch size (what round 1 shipped), kept as the small-launch path"""
+    _run({"ITB_ATTN_BULK": "0"}, "full_size", path="tests/test_gpu_decode.py")
