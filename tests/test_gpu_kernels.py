@@ -174,10 +174,12 @@ def test_embed_ln_and_add_ln(dtype):
 
 # ------------------------------------------------------------------------------------------------ attention
 @pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16, _lib.F16])
-@pytest.mark.parametrize("step,T,beam", [(1, 48, 4), (2, 48, 4), (40, 48, 4), (9, 12, 4), (120, 130, 4), (70, 80, 5)])
+@pytest.mark.parametrize("step,T,beam", [(1, 48, 4), (2, 48, 4), (40, 48, 4), (9, 12, 4), (120, 130, 4), (70, 80, 5),
+                                         (100, 112, 8), (170, 352, 12), (300, 320, 12), (33, 48, 1)])
 def test_self_attention_through_ancestor_table(dtype, step, T, beam):
     """T = 12: ancestor table shorter than a warp; step 120: up to 480 virtual positions (many copy stages, table reads
-    past the 32 positions held in registers); beam 5: a second group of one slot per sentence."""
+    past the 32 positions held in registers); beam 5: a second group of one slot per sentence; beam 8 / 12: two / three full
+    groups per sentence at long contexts (BASELINE configs[3] shapes); beam 1: greedy."""
     B, d, H = 3, 768, 12
     M, pc = B * beam, step - 1
     act = ACT[dtype]
@@ -217,7 +219,7 @@ def test_self_attention_through_ancestor_table(dtype, step, T, beam):
 
 @pytest.mark.parametrize("dtype", [_lib.F32, _lib.BF16, _lib.F16])
 @pytest.mark.parametrize("masked", [False, True])
-@pytest.mark.parametrize("S,beam", [(21, 4), (100, 4), (77, 5)])
+@pytest.mark.parametrize("S,beam", [(21, 4), (100, 4), (77, 5), (256, 12), (130, 8), (49, 1)])
 def test_cross_attention_with_additive_mask(dtype, masked, S, beam):
     """S = 100 / 77: several copy stages with a partial last chunk (the K / V pipeline of the tensor-core kernel);
     beam 5: a second group of one slot per sentence."""
