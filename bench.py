@@ -47,7 +47,8 @@ def parse():
     ap.add_argument("--lanes", type=int, default=2, help="super-batches in flight per GPU (separate streams)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the per-batch / GPU-eager / extra roofline legs")
-    ap.add_argument("--cpu-sentences", type=int, default=16)
+    ap.add_argument("--cpu-sentences", type=int, default=12)
+    ap.add_argument("--eos-bias", type=float, default=0.0, help="added to the EOS logit bias: > 0 makes hypotheses finish early (random-init weights never emit EOS on their own, so the default workload runs every sentence to its max_len)")
     ap.add_argument("--cpu-full", action="store_true", help="cpu baseline on the FULL median batch (minutes)")
     ap.add_argument("--no-gather", action="store_true", help="diagnostic: leave the NCCL output gather out of the passes (N > 1)")
     return ap.parse_args()
@@ -335,6 +336,10 @@ def make_text_model(args, dev):
     from imagetranslate_b200.models import MassSeq2Seq, SyntheticTextProcessor
     torch.manual_seed(0)
     model = MassSeq2Seq(SyntheticTextProcessor(VOCAB), lang_dec=False, tie_embed=False, enc_layer=ENC, dec_layer=DEC).eval()
+    if args.eos_bias != 0.0:
+        with torch.no_grad():
+            for ol in model.output_layer:
+                ol.layer.bias[4] += args.eos_bias
     model = model.to(dev)
     if args.dtype != "fp32":
         model = model.to(torch.bfloat16)
@@ -404,6 +409,7 @@ def run_text(args, rank, world, local_rank):
                    "arithmetic": {"fp16": "bf16-valued model weights held exactly in fp16; fp16 x fp16 -> fp32 tcgen05 MMAs, fp16 activations / KV cache, fp32 softmax / LayerNorm / logits / scores",
                                   "bf16": "bf16 weights, activations and KV cache; fp32 accumulation, softmax, LayerNorm, logits, scores",
                                   "fp32": "fp32 parity kernels (CUDA cores)"}[args.dtype],
+                   "eos_bias": args.eos_bias,
                    "value_includes": "encoder + cross-KV + every search step + extraction" + (" + NCCL output gather" if world > 1 else ""),
                    "l2": "working set > L2: 191 MB of 16-bit weights streamed every search step plus the KV cache",
                    "parallelism": "dp%d (whole batches per rank, one all-gather of outputs at the end of every pass)" % world},

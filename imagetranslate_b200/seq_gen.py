@@ -294,8 +294,11 @@ class BeamDecoder(nn.Module):
     def forward_many(self, batches, lanes: int = 2, rows: int = 1024):
         """Decodes a list of batches (each a dict of `forward` keyword arguments) and returns their outputs in order.
 
-        Every batch is decoded exactly as `forward` would decode it (same loop bound, termination rule and arithmetic
-        per reference batch, so results do not depend on `lanes` / `rows`), but
+        Every batch is decoded exactly as `forward` would decode it (same loop bound, termination rule and memory per
+        reference batch).  In the fp32 parity mode the results are invariant to `lanes` and `rows`; in the 16-bit modes they are
+        deterministic for a fixed `rows` and independent of `lanes`, but NOT invariant to `rows`: the GEMM tile height,
+        split-K factor and attention staging are chosen by launch size, so the summation order -- and with it the winner of a
+        near-tie -- can change with the super-batch size.  Otherwise:
           * consecutive compatible batches are decoded in lockstep as one SUPER-BATCH of up to `rows` beam rows: one
             kernel chain and one pass over the 191 MB of decoder + vocabulary weights per step serves all of them
             (a single reference batch at --batch 4000 has 120-940 rows and leaves the step latency-bound);
