@@ -189,27 +189,33 @@ def gpu_eager_baseline(args, dev):
 
 
 # ------------------------------------------------------------------------------------------- kernel rooflines
-def _time_launches(fn, n=20, flush=None):
-    for _ in range(3):
-        fn()
-    tot = 0.0
-    for _ in range(n):
-        if flush is not None:
-            flush.zero_()                   # L2 flush between timed launches
-        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
-        e0.record(); fn(); e1.record(); e1.synchronize()
-        tot += e0.elapsed_time(e1)
-    return tot / n
+def _time_rotating(fn, n_sets, reps=3):
+    """Average duration of one launch of fn(i), i cycling over `n_sets` operand sets whose cold part (weights / K,V cache)
+    adds up to more than the 126 MB L2, launched back to back on the current stream and timed with CUDA events around
+    the whole train (>= 2 warm-up trains first).  Every launch therefore streams its weights / cache from HBM, as in a
+    search step, while its small activation operands stay L2-resident, as in a search step."""
+    for _ in range(2):
+        for i in range(n_sets):
+            fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    e0.record()
+    for _ in range(reps):
+        for i in range(n_sets):
+            fn(i)
+    e1.record()
+    e1.synchronize()
+    return e0.elapsed_time(e1) / (reps * n_sets)
 
 
 def time_kernel_rooflines(gen, model, peaks, rows, code, extras=True):
-    """Times the dominant kernels of the search step ALONE at the super-batch row count, with CUDA events on the launching
-    stream and L2 flushed between launches:
-      roofline            the fused vocabulary projection (tcgen05 GEMM whose epilogue emits the softmax / top-k partials),
-                          tensor-bound: algorithmic flops = 2 * rows * V * d
+    """Times the dominant kernels of the search step at the super-batch row count, each as a train of back-to-back launches
+    over rotating operand sets larger than L2 (see _time_rotating), CUDA events on the launching stream:
+      roofline              the fused vocabulary projection (tcgen05 GEMM whose epilogue emits the softmax / top-k partials),
+                            tensor-bound: algorithmic flops = 2 * rows * V * d
       roofline_gemm_layers  the four layer-GEMM shapes of a decoder layer (QKV, O = CQ = CO, FFN1 + GELU, FFN2), tensor
-      roofline_attention  cross-attention over S = 100 memory positions and self-attention at t = 80, HBM-bound:
-                          algorithmic bytes = K,V rows that must be read once"""
+      roofline_attention    cross-attention over S = 100 memory positions and self-attention at t = 80, HBM-bound:
+                            algorithmic bytes = K,V rows that must be read once"""
     import ctypes as C
     from imagetranslate_b200 import _lib
     dev = torch.device("cuda", torch.cuda.current_device())
@@ -223,15 +229,18 @@ def time_kernel_rooflines(gen, model, peaks, rows, code, extras=True):
     cand_idx = torch.empty(M, nc, KT, dtype=torch.int32, device=dev)
     cmax, csum = torch.empty(M, nc, device=dev), torch.empty(M, nc, device=dev)
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     peak = peaks.get("bf16_tflops", 1590.0)
     hbm = peaks.get("hbm_gbs", 6550.0)
+    copies = lambda t, total_mb: [t] + [t.clone() for _ in range(max(1, int(total_mb * 1e6 / (t.numel() * t.element_size()))) )]
 
-    def vocab():
-        _lib.check(lib.itb_vocab_partials(code, BEAM, _lib.ptr(x), _lib.ptr(pw.w_vocab), _lib.ptr(pw.b_vocab), M, V, d,
+    wv = copies(pw.w_vocab, 190)                 # 92 MB each: 3 copies
+
+    def vocab(i):
+        _lib.check(lib.itb_vocab_partials(code, BEAM, _lib.ptr(x), _lib.ptr(wv[i]), _lib.ptr(pw.b_vocab), M, V, d,
                                           _lib.ptr(cand_val), _lib.ptr(cand_idx), _lib.ptr(cmax), _lib.ptr(csum), None, stream))
 
-    ms = _time_launches(vocab, 20, flush)
+    ms = _time_rotating(vocab, len(wv), 4)
+    del wv
     tf = 2.0 * M * V * d / ms / 1e9
     traffic = None
     try:        # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at this shape, from the committed ncu capture
@@ -243,10 +252,11 @@ def time_kernel_rooflines(gen, model, peaks, rows, code, extras=True):
     alg = V * d * 2 + M * d * 2 + M * nc * (2 + 2 * KT) * 4
     out = {"roofline": dict(bound="tensor", achieved=tf, peak=peak, unit="TFLOP/s", frac=tf / peak, traffic=traffic,
                             kernel="gemm_tc_kernel<256, vocab-partials> rows=%d V=%d K=%d (fused logits + softmax/top-k partials)" % (M, V, d),
-                            ms=ms, algorithmic_bytes=alg, hbm_gbs_at_algorithmic_bytes=alg / ms / 1e6)}
+                            ms=ms, algorithmic_bytes=alg, hbm_gbs_at_algorithmic_bytes=alg / ms / 1e6,
+                            protocol="train of launches over 3 rotating weight copies (276 MB > L2), CUDA events on the launching stream")}
     if not extras:
         return out
-    # ---- layer GEMMs
+    # ---- layer GEMMs: weights rotate over > 160 MB of copies (cold, as between two search steps), activations stay hot
     gl = {}
     ly = pw.keep[0]
     y = torch.empty(_lib.Y_PARTIALS * M * max(3 * d, F), dtype=torch.float32, device=dev)
@@ -255,41 +265,45 @@ def time_kernel_rooflines(gen, model, peaks, rows, code, extras=True):
                                      ("o_cq_co", ly["w_o"], ly["b_o"], x, d, d, _lib.EPI_BIAS_F32),
                                      ("ffn1_gelu", ly["w_1"], ly["b_1"], x, F, d, _lib.EPI_BIAS_GELU_ACT),
                                      ("ffn2", ly["w_2"], ly["b_2"], hbuf, d, F, _lib.EPI_BIAS_F32)):
-        fn = lambda w=w, b=b, a=a, N=N, K=K, epi=epi: _lib.check(lib.itb_linear(code, _lib.GEMM_AUTO, epi, _lib.ptr(a), _lib.ptr(w),
-                                                                                _lib.ptr(b), _lib.ptr(y), M, N, K, N, stream))
-        t = _time_launches(fn, 20, flush)
+        ws_ = copies(w, 160)
+        fn = lambda i, ws_=ws_, b=b, a=a, N=N, K=K, epi=epi: _lib.check(lib.itb_linear(code, _lib.GEMM_AUTO, epi, _lib.ptr(a), _lib.ptr(ws_[i]),
+                                                                                       _lib.ptr(b), _lib.ptr(y), M, N, K, N, stream))
+        t = _time_rotating(fn, len(ws_), 2)
         f = 2.0 * M * N * K / t / 1e9
-        gl[name] = dict(ms=t, achieved=f, frac=f / peak, shape="M=%d N=%d K=%d" % (M, N, K))
+        gl[name] = dict(ms=t, achieved=f, frac=f / peak, shape="M=%d N=%d K=%d" % (M, N, K), weight_copies=len(ws_))
+        del ws_
     tot_ms = gl["qkv"]["ms"] + 3 * gl["o_cq_co"]["ms"] + gl["ffn1_gelu"]["ms"] + gl["ffn2"]["ms"]
     tot_fl = 2.0 * M * (6 * d * d + 2 * d * F)
     out["roofline_gemm_layers"] = dict(bound="tensor", unit="TFLOP/s", peak=peak, achieved=tot_fl / tot_ms / 1e9,
                                        frac=tot_fl / tot_ms / 1e9 / peak, per_shape=gl,
-                                       note="one decoder layer's six GEMMs (QKV + O + CQ + CO + FFN1 + FFN2), each timed alone, L2 flushed")
-    # ---- attention (HBM)
-    B, S, t_pos, T = M // BEAM, 100, 80, 160
+                                       note="one decoder layer's six GEMMs (QKV + O + CQ + CO + FFN1 + FFN2); each shape a train of launches over rotating weight copies > L2")
+    # ---- attention (HBM): 4 rotating K,V buffers of 0.3 GB each
+    B, S, t_pos, T = M // BEAM, 100, 80, 96
     esz = 2
     ctl = torch.tensor([t_pos, 0, t_pos - 1, 0, 0, 0, 1000, 0], dtype=torch.int32, device=dev)
     qkv = torch.randn(M, 3 * d, device=dev)
-    ckv = torch.randn(B, S, 1, 2, d, device=dev).to(act)
+    ckv = [torch.randn(B, S, 1, 2, d, device=dev).to(act) for _ in range(4)]
     mask = torch.ones(B, S, dtype=torch.uint8, device=dev)
     ctx = torch.empty(M, d, dtype=act, device=dev)
-    cross = lambda: _lib.check(lib.itb_cross_attention(code, _lib.ptr(ctl), None, None, _lib.ptr(qkv), 3 * d, _lib.ptr(ckv), 0, _lib.ptr(mask),
-                                                       _lib.ptr(ctx), M, BEAM, d, H, S, 1, stream))
-    t_c = _time_launches(cross, 20, flush)
+    cross = lambda i: _lib.check(lib.itb_cross_attention(code, _lib.ptr(ctl), None, None, _lib.ptr(qkv), 3 * d, _lib.ptr(ckv[i]), 0, _lib.ptr(mask),
+                                                         _lib.ptr(ctx), M, BEAM, d, H, S, 1, stream))
+    t_c = _time_rotating(cross, 4, 4)
     by_c = B * S * 2 * d * esz
-    kv = torch.randn(M, T, 2, d, device=dev).to(act)
+    del ckv
+    kv = [torch.randn(M, T, 2, d, device=dev).to(act) for _ in range(2)]         # 1.2 GB each
     anc = torch.randint(0, BEAM, (2, M, T), device=dev)
     share = t_pos - 6                  # hypotheses of a sentence share their prefix up to the last few positions
     anc[:, :, :share] = anc.view(2, B, BEAM, T)[:, :, :1, :share].expand(2, B, BEAM, share).reshape(2, M, share)
     anc = anc.to(torch.uint8)
-    self_ = lambda: _lib.check(lib.itb_self_attention(code, _lib.ptr(ctl), None, _lib.ptr(qkv), _lib.ptr(kv), _lib.ptr(anc), _lib.ptr(ctx),
-                                                      M, BEAM, d, H, T, stream))
-    t_s = _time_launches(self_, 20, flush)
+    self_ = lambda i: _lib.check(lib.itb_self_attention(code, _lib.ptr(ctl), None, _lib.ptr(qkv), _lib.ptr(kv[i]), _lib.ptr(anc), _lib.ptr(ctx),
+                                                        M, BEAM, d, H, T, stream))
+    t_s = _time_rotating(self_, 2, 6)
     by_s = (B * share + M * (t_pos - share)) * 2 * d * esz
     out["roofline_attention"] = dict(bound="hbm", unit="GB/s", peak=hbm, achieved=by_c / t_c / 1e6, frac=by_c / t_c / 1e6 / hbm,
-                                     kernel="cross-attention, %d sentences x S=%d (one layer)" % (B, S), ms=t_c, algorithmic_bytes=by_c,
+                                     kernel="cross-attention (attn_bulk_kernel: cp.async.bulk + mbarrier ring), %d sentences x S=%d, one layer" % (B, S),
+                                     ms=t_c, algorithmic_bytes=by_c, protocol="train of launches over 4 rotating K,V buffers (1.26 GB > L2)",
                                      self_attention=dict(ms=t_s, algorithmic_bytes=by_s, achieved=by_s / t_s / 1e6, frac=by_s / t_s / 1e6 / hbm,
-                                                         kernel="self-attention t=%d, %d rows, prefix shared up to position %d" % (t_pos, M, share)))
+                                                         kernel="self-attention (attn_mma_kernel) t=%d, %d rows, prefix shared up to position %d" % (t_pos, M, share)))
     return out
 
 
@@ -426,7 +440,7 @@ def run_text(args, rank, world, local_rank):
         extras = world == 1 and not args.no_extras
         if args.dtype != "fp32":
             line.update(time_kernel_rooflines(gen, model, peaks, args.rows, code, extras))
-            line["roofline"]["peak_source"] = "MEASURED_PEAKS.json bf16_tflops (burst, kernel timed alone)" if peaks else "fallback 1590 TFLOP/s"
+            line["roofline"]["peak_source"] = "MEASURED_PEAKS.json bf16_tflops (burst, kernel timed alone) / hbm_gbs" if peaks else "fallback 1590 TFLOP/s, 6550 GB/s"
         if extras and args.config == 2:
             # the reference driver's call pattern: generator(...) once per reference batch (src/translate.py:46-49)
             def per_batch():
