@@ -54,9 +54,9 @@ def parse():
     return ap.parse_args()
 
 
-def build_batches(n_sent, seed, batch, capacity, min_len=16, max_len=128):
+def build_batches(n_sent, seed, batch, capacity, min_len=16, max_len=128, body_seed=None):
     from imagetranslate_b200.dataset import MTDataset, synthetic_sentences
-    sents = synthetic_sentences(n_sent, VOCAB, min_len, max_len, seed=seed)
+    sents = synthetic_sentences(n_sent, VOCAB, min_len, max_len, seed=seed, body_seed=body_seed)
     ex = [(s, [6], 0, 1) for s in sents]
     return MTDataset(examples=ex, max_batch_capacity=capacity, max_batch=batch, pad_idx=0, max_seq_len=10000).batches
 
@@ -384,10 +384,11 @@ def run_text(args, rank, world, local_rank):
             n_total, args.batch, args.capacity, world, len(batches))
     else:
         n_sent = args.sentences or 4096
-        batches = build_batches(n_sent, 1234 + rank, args.batch, args.capacity)
+        # every rank decodes its OWN sentences (token bodies drawn per rank) of the SAME length multiset: equal work per rank
+        batches = build_batches(n_sent, 1234, args.batch, args.capacity, body_seed=None if rank == 0 else 5000 + rank)
         ids = [rank * n_sent + k for k in range(n_sent)]
         n_total = n_sent * world
-        workload = "configs[1]: MassSeq2Seq base V=60000 6+6 d=768 beam 4, %d synthetic sentences/rank len 16-128 length-sorted, --batch %d --capacity %d (%d batches/rank), random-init weights" % (
+        workload = "configs[1]: MassSeq2Seq base V=60000 6+6 d=768 beam 4, %d synthetic sentences/rank len 16-128 length-sorted (same length multiset, different sentences on every rank), --batch %d --capacity %d (%d batches/rank), random-init weights" % (
             n_sent, args.batch, args.capacity, len(batches))
     host_kw = [batch_kwargs(b, pin=True) for b in batches]
     dev_kw = [batch_kwargs(b, device=dev) for b in batches]

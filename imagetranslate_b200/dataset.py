@@ -61,16 +61,19 @@ class MTDataset(torch.utils.data.Dataset):
         return self.batches[item]
 
 
-def synthetic_sentences(n, vocab, min_len=16, max_len=128, seed=1234, lang_token=5, eos=4, sort=True):
+def synthetic_sentences(n, vocab, min_len=16, max_len=128, seed=1234, lang_token=5, eos=4, sort=True, body_seed=None):
     """BASELINE.json configs[1]: lengths ~U{min..max} incl. the leading language token and trailing </s>,
-    body tokens ~U{7..V-1}; length-sorted like the reference's training binariser (src/create_mt_batches.py:30-40)."""
+    body tokens ~U{7..V-1}; length-sorted like the reference's training binariser (src/create_mt_batches.py:30-40).
+    `body_seed` draws the token bodies from a second generator, so that several ranks can decode DIFFERENT sentences of
+    the SAME length multiset (equal work per rank: what a weak-scaling run should compare)."""
     g = torch.Generator().manual_seed(seed)
     lens = torch.randint(min_len, max_len + 1, (n,), generator=g)
     if sort:
         lens, _ = torch.sort(lens)
+    gb = g if body_seed is None else torch.Generator().manual_seed(body_seed)
     out = []
     for L in lens.tolist():
-        body = torch.randint(7, vocab, (L,), generator=g)
+        body = torch.randint(7, vocab, (L,), generator=gb)
         body[0], body[-1] = lang_token, eos
         out.append(body)
     return out

@@ -124,3 +124,37 @@ def test_two_rank_sharded_decode_equals_single_rank(dtype):
         p.join(timeout=120)
         assert p.exitcode == 0
     assert got == single
+
+
+@two_gpus
+def test_translate_driver_under_torchrun_writes_the_single_gpu_file(tmp_path):
+    """python -m imagetranslate_b200.translate on 2 ranks (whole batches assigned by cost, ONE gather, rank 0 writes) must
+    write the same file as the single-process run (BASELINE configs[0] tokenizer / input, a small seeded model)."""
+    import subprocess
+    import sys
+    import types
+    from imagetranslate_b200 import translate as tr
+    from imagetranslate_b200.models import Seq2Seq
+    from imagetranslate_b200.textprocessor import TextProcessor
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "config1")
+    tp = TextProcessor(gold)
+    torch.manual_seed(3)
+    model = Seq2Seq(tp, lang_dec=False, tie_embed=False, enc_layer=1, dec_layer=1)
+    with torch.no_grad():
+        model.output_layer[0].layer.bias[4] += 1.0
+    model_dir = str(tmp_path / "model")
+    model.save(model_dir)
+    common = ["--tok", gold, "--model", model_dir, "--input", os.path.join(gold, "input.txt"), "--src", "fa", "--target", "en",
+              "--beam", "4", "--batch", "400", "--capacity", "600"]          # --batch 400: several batches to shard
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    one = str(tmp_path / "one.txt")
+    r = subprocess.run([sys.executable, "-m", "imagetranslate_b200.translate", "--output", one] + common, cwd=root,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    two = str(tmp_path / "two.txt")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", str(_free_port()), "-m", "imagetranslate_b200.translate", "--output", two] + common,
+                       cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    a, b = open(one).read(), open(two).read()
+    assert len(a) > 100 and a == b
