@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--cpu-sentences", type=int, default=12)
     ap.add_argument("--eos-bias", type=float, default=0.0, help="added to the EOS logit bias: > 0 makes hypotheses finish early (random-init weights never emit EOS on their own, so the default workload runs every sentence to its max_len)")
     ap.add_argument("--cpu-full", action="store_true", help="cpu baseline on the FULL median batch (minutes)")
+    ap.add_argument("--single-leg", action="store_true", help="time ONE leg only, from pinned host inputs (value = e2e); for the long config-5 passes")
     ap.add_argument("--no-gather", action="store_true", help="diagnostic: leave the NCCL output gather out of the passes (N > 1)")
     return ap.parse_args()
 
@@ -391,7 +392,7 @@ def run_text(args, rank, world, local_rank):
         workload = "configs[1]: MassSeq2Seq base V=60000 6+6 d=768 beam 4, %d synthetic sentences/rank len 16-128 length-sorted (same length multiset, different sentences on every rank), --batch %d --capacity %d (%d batches/rank), random-init weights" % (
             n_sent, args.batch, args.capacity, len(batches))
     host_kw = [batch_kwargs(b, pin=True) for b in batches]
-    dev_kw = [batch_kwargs(b, device=dev) for b in batches]
+    dev_kw = [] if args.single_leg else [batch_kwargs(b, device=dev) for b in batches]
     h2d = sum(sum(v.numel() * v.element_size() for v in kw.values() if torch.is_tensor(v)) for kw in host_kw)
     gathered = {}
 
@@ -410,8 +411,12 @@ def run_text(args, rank, world, local_rank):
         return toks, n_launch
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
-    ms, toks, launches, clocks = _timed(lambda: one_pass(dev_kw), args.steps, args.warmup, dev, world, sampler)
-    ms_e, toks_e, _, _ = _timed(lambda: one_pass(host_kw), args.steps, 1, dev, world)
+    if args.single_leg:
+        ms, toks, launches, clocks = _timed(lambda: one_pass(host_kw), args.steps, args.warmup, dev, world, sampler)
+        ms_e, toks_e = ms, toks
+    else:
+        ms, toks, launches, clocks = _timed(lambda: one_pass(dev_kw), args.steps, args.warmup, dev, world, sampler)
+        ms_e, toks_e, _, _ = _timed(lambda: one_pass(host_kw), args.steps, 1, dev, world)
     if world > 1 and rank == 0 and not args.no_gather:
         assert gathered["n"] == n_total, "gather returned %d of %d sentences" % (gathered["n"], n_total)
         assert gathered["tokens"] * args.steps == int(toks_e), "gathered token count differs from the ranks' own"
@@ -424,7 +429,7 @@ def run_text(args, rank, world, local_rank):
                    "arithmetic": {"fp16": "bf16-valued model weights held exactly in fp16; fp16 x fp16 -> fp32 tcgen05 MMAs, fp16 activations / KV cache, fp32 softmax / LayerNorm / logits / scores",
                                   "bf16": "bf16 weights, activations and KV cache; fp32 accumulation, softmax, LayerNorm, logits, scores",
                                   "fp32": "fp32 parity kernels (CUDA cores)"}[args.dtype],
-                   "eos_bias": args.eos_bias,
+                   "eos_bias": args.eos_bias, "single_leg": bool(args.single_leg),
                    "value_includes": "encoder + cross-KV + every search step + extraction" + (" + NCCL output gather" if world > 1 else ""),
                    "l2": "working set > L2: 191 MB of 16-bit weights streamed every search step plus the KV cache",
                    "parallelism": "dp%d (whole batches per rank, one all-gather of outputs at the end of every pass)" % world},
