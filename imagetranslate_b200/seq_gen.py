@@ -326,6 +326,24 @@ class BeamDecoder(nn.Module):
                 results[i] = o
 
         lanes = max(1, min(int(lanes), len(packs)))
+        if lanes > 1:
+            # longest super-batch first: the lanes take super-batches from one queue, so the last one to start should be
+            # the shortest, or one lane ends up decoding the most expensive super-batch alone (results are stored by batch
+            # index and do not depend on the order)
+            from .parallel import batch_cost
+
+            def cost(idxs):
+                c = 0.0
+                for i in idxs:
+                    kw = batches[i]
+                    src = self._unwrap(kw.get("src_inputs"))
+                    n = int(self._unwrap(kw["first_tokens"]).numel())
+                    S = int(src.size(1)) if src is not None else 49
+                    c += batch_cost(n, S, kw.get("beam_width") or self.beam_width, self.max_len_a, self.max_len_b) if kw.get("max_len") is None \
+                        else float(kw["max_len"]) * n
+                return c
+
+            packs = sorted(packs, key=lambda idxs: (-cost(idxs), idxs[0]))
         if lanes == 1:
             for idxs in packs:
                 run_pack(idxs)
