@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--capacity", type=int, default=600)
     ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16", "fp32"])
     ap.add_argument("--rows", type=int, default=4096, help="beam rows per super-batch (consecutive reference batches decoded in lockstep)")
-    ap.add_argument("--lanes", type=int, default=2, help="super-batches in flight per GPU (separate streams)")
+    ap.add_argument("--lanes", type=int, default=3, help="super-batches in flight per GPU (separate streams)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the per-batch / GPU-eager / extra roofline legs")
     ap.add_argument("--cpu-sentences", type=int, default=12)

@@ -35,7 +35,7 @@ def get_lm_option_parser():
     parser.add_option("--obj", action="store_true", dest="obj", default=False)
     # additions of this driver
     parser.add_option("--rows", dest="rows", help="beam rows per super-batch", type="int", default=4096)
-    parser.add_option("--lanes", dest="lanes", help="super-batches in flight per GPU", type="int", default=2)
+    parser.add_option("--lanes", dest="lanes", help="super-batches in flight per GPU", type="int", default=3)
     parser.add_option("--window", dest="window", help="image batches handed to the decoder at once", type="int", default=64)
     return parser
 
@@ -61,7 +61,7 @@ def caption_batch(batch, generator, text_processor):
     return [text_processor.tokenizer.decode(x[1:].numpy()) for x in outputs], batch["paths"]
 
 
-def caption_batches(batches, generator, text_processor, rows=4096, lanes=2):
+def caption_batches(batches, generator, text_processor, rows=4096, lanes=3):
     outs = generator.forward_many([batch_kwargs(b, text_processor) for b in batches], lanes=lanes, rows=rows)
     return [([text_processor.tokenizer.decode(x[1:].numpy()) for x in o], _paths(b)) for b, o in zip(batches, outs)]
 

@@ -291,7 +291,7 @@ class BeamDecoder(nn.Module):
             packs.append(cur)
         return packs
 
-    def forward_many(self, batches, lanes: int = 2, rows: int = 1024):
+    def forward_many(self, batches, lanes: int = 3, rows: int = 4096):
         """Decodes a list of batches (each a dict of `forward` keyword arguments) and returns their outputs in order.
 
         Every batch is decoded exactly as `forward` would decode it (same loop bound, termination rule and memory per

@@ -45,7 +45,7 @@ def get_lm_option_parser():
     parser.add_option("--fp16", action="store_true", dest="fp16", default=False)
     # additions of this driver (defaults keep the reference's results)
     parser.add_option("--rows", dest="rows", help="beam rows per super-batch", type="int", default=4096)
-    parser.add_option("--lanes", dest="lanes", help="super-batches in flight per GPU", type="int", default=2)
+    parser.add_option("--lanes", dest="lanes", help="super-batches in flight per GPU", type="int", default=3)
     parser.add_option("--window", dest="window", help="batches handed to the decoder at once", type="int", default=96)
     return parser
 
@@ -73,7 +73,7 @@ def translate_batch(batch, generator, text_processor, verbose=False):
     return mt_output, src_text
 
 
-def translate_batches(batches, generator, text_processor, verbose=False, rows=4096, lanes=2):
+def translate_batches(batches, generator, text_processor, verbose=False, rows=4096, lanes=3):
     """A window of DataLoader items through `forward_many`; returns [(mt_output, src_text)] per batch, in order."""
     kws = [batch_kwargs(b, text_processor) for b in batches]
     outs = generator.forward_many(kws, lanes=lanes, rows=rows)
