@@ -19,7 +19,7 @@ P = C.c_void_p
 
 
 class Ctl(C.Structure):
-    _fields_ = [(n, C.c_int) for n in ("step", "done", "steps_run", "cur", "fin_rows", "sent_done", "max_len", "pad_")]
+    _fields_ = [(n, C.c_int) for n in ("step", "done", "steps_run", "cur", "fin_rows", "sent_done", "max_len", "rows_active")]
 
 
 class Grp(C.Structure):

@@ -486,10 +486,16 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
         }
     }
     __syncthreads();
-    for (int i = tid; i < a.B; i += blockDim.x)
+    __shared__ int s_hi;                 // 1 + index of the last sentence whose group is still searching
+    if (tid == 0) s_hi = 0;
+    __syncthreads();
+    for (int i = tid; i < a.B; i += blockDim.x) {
         if (a.sent_done[i] == 0 && a.grp[a.sent_grp[i]].done != 0) a.sent_done[i] = 1;
+        if (a.sent_done[i] == 0) atomicMax(&s_hi, i + 1);
+    }
     __syncthreads();
     if (tid == 0) {
+        ctl->rows_active = max(s_hi, 1) * a.beam;
         ctl->steps_run = step;
         ctl->step = step + 1;
         ctl->cur = nxt;

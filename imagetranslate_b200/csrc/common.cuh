@@ -19,7 +19,8 @@ struct ItbCtl {
     int fin_rows;    // rows (over the whole batch) whose prefix holds an EOS
     int sent_done;   // sentences that finished the merge phase of the current step
     int max_len;     // loop bound of :131 (steps run for i in [1, max_len))
-    int pad_;
+    int rows_active; // rows [rows_active, M) belong to groups whose search has ended (groups are laid out longest loop bound
+                     // first, so finished rows form a suffix): the dense kernels skip them.  <= 0: unset, every row is live
 };
 
 // Programmatic dependent launch (PDL).  Every kernel of the step chain is launched with the programmatic-stream-
@@ -37,6 +38,13 @@ struct ItbGrp {
     int final_cur;   // ping-pong parity holding the group's final state
     int pad0_, pad1_;
 };
+
+// rows the dense kernels still have to compute (see ItbCtl::rows_active)
+__device__ __forceinline__ int itb_rows_active(const ItbCtl* ctl) {
+    if (ctl == nullptr) return 0x7fffffff;
+    const int ra = ctl->rows_active;
+    return ra > 0 ? ra : 0x7fffffff;
+}
 
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }

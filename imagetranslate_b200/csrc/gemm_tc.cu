@@ -166,6 +166,15 @@ __device__ __forceinline__ void tc_tile_of(int t, int nsplit, int m_tiles, int n
     else { mt = u % m_tiles; nt = u / m_tiles; }
 }
 
+// Rows [rows_act, rows) of the activation operand belong to groups whose search has ended (ItbCtl::rows_active): a tile
+// whose activation rows all lie there is skipped -- by EVERY role of the CTA alike (they walk the same filtered tile list).
+template <bool SWAPPED>
+__device__ __forceinline__ bool tc_tile_dead(int t, int nsplit, int m_tiles, int n_tiles, int mt_rows, int rows_act) {
+    int ks, mt, nt;
+    tc_tile_of<SWAPPED>(t, nsplit, m_tiles, n_tiles, ks, mt, nt);
+    return SWAPPED ? (nt * TC_BN >= rows_act) : (mt * mt_rows >= rows_act);
+}
+
 // Output of the fused vocabulary projection (EPI >= ITB_EPI_VOCAB_K4): per (decoder row, chunk of 128 vocabulary
 // entries) the chunk's max logit, sum exp(logit - max) and top-KT (logit, index) -- what the beam kernel needs to finish
 // log_softmax + top-k (reference src/seq_gen.py:194,203) without an (M,V) logits tensor ever reaching HBM.
@@ -246,7 +255,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 template <int MT, bool PAIR = false>
 __device__ __forceinline__ void tc_epilogue_vocab4(uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty, const float* __restrict__ bias,
                                                   const TcVocabPart vp, int V, int rows, int total, int m_tiles, int n_tiles,
-                                                  int warp, int lane, float* cbuf, uint32_t tempty_remote = 0u) {
+                                                  int warp, int lane, float* cbuf, uint32_t tempty_remote = 0u, int rows_act = 0x7fffffff) {
     static_assert(MT == 256, "the vocabulary epilogue is written for 256-entry tiles");
     constexpr int KT = 4;
     static_assert(2 + 2 * KT <= TC_CAND_SLOTS, "the exchange of the partials uses the candidate slots");
@@ -262,6 +271,7 @@ __device__ __forceinline__ void tc_epilogue_vocab4(uint32_t tmem_base, uint64_t*
     for (int t = t0; t < total; t += tstep) {
         int ks, mt, nt;
         tc_tile_of<true>(t, 1, m_tiles, n_tiles, ks, mt, nt);
+        if (!PAIR && nt * TC_BN >= rows_act) continue;              // rows of finished groups only (see tc_tile_dead)
         if (PAIR) nt = 2 * nt + (int)(blockIdx.x & 1);
         mbar_wait(&tfull[as], aphase);
         tc_fence_after();
@@ -425,7 +435,7 @@ __device__ __forceinline__ void tc_epilogue_vocab4(uint32_t tmem_base, uint64_t*
 template <int MT, int KT, bool PAIR = false>
 __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty, const float* __restrict__ bias,
                                                   const TcVocabPart vp, int V, int rows, int total, int m_tiles, int n_tiles,
-                                                  int warp, int lane, uint32_t tempty_remote = 0u) {
+                                                  int warp, int lane, uint32_t tempty_remote = 0u, int rows_act = 0x7fffffff) {
     static_assert(MT == 256, "the vocabulary epilogue is written for 256-entry tiles");
     constexpr float kLog2e = 1.4426950408889634f;
     const int q = warp & 3, half = (warp - 4) >> 2;
@@ -434,6 +444,7 @@ __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* 
     for (int t = t0; t < total; t += tstep) {
         int ks, mt, nt;
         tc_tile_of<true>(t, 1, m_tiles, n_tiles, ks, mt, nt);
+        if (!PAIR && nt * TC_BN >= rows_act) continue;              // rows of finished groups only (see tc_tile_dead)
         if (PAIR) nt = 2 * nt + (int)(blockIdx.x & 1);
         mbar_wait(&tfull[as], aphase);
         tc_fence_after();
@@ -524,13 +535,14 @@ __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* 
 template <int MT, int EPI, typename OT>
 __device__ __forceinline__ void tc_epilogue(uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty, const float* __restrict__ bias,
                                             OT* __restrict__ out, int M, int N, int ldo, int nsplit, size_t part_stride,
-                                            int total, int m_tiles, int warp, int lane) {
+                                            int total, int m_tiles, int warp, int lane, int rows_act) {
     const int q = warp & 3;                                 // TMEM lane quarter this warp may access
     const int half = (warp - 4) >> 2;                       // which half of the tile's columns this warp drains
     constexpr int CH = (MT / 2 < 32) ? 32 : MT / 2;         // MT = 32: the second warp of the quarter has no columns
     uint32_t as = 0, aphase = 0;
     for (int t = blockIdx.x; t < total; t += gridDim.x) {
         const int ks = t % nsplit, mt = (t / nsplit) % m_tiles, nt = (t / nsplit) / m_tiles;
+        if (mt * MT >= rows_act) continue;                  // rows of finished groups only (see tc_tile_dead)
         mbar_wait(&tfull[as], aphase);
         tc_fence_after();
         const int n = nt * TC_BN + q * 32 + lane;
@@ -609,17 +621,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"((uint32_t)Cfg::kTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    // Live rows of the activation operand.  Read BEFORE the programmatic-dependency wait, once per CTA, and shared by all
+    // roles: the value may lag the current step (the beam kernel of the previous step may still be in flight), which is
+    // safe -- rows_active never grows during a (super-)batch, so a stale value only keeps a few finished rows alive -- and
+    // it lets the producer pick its first tile, whose weights it streams ahead of the wait, from the live ones.
+    if (threadIdx.x == 96) tmem_slot[1] = (uint32_t)itb_rows_active(ctl);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    const int rows_act = (int)tmem_slot[1];
+    int tfirst = blockIdx.x;                           // this CTA's first live tile
+    while (tfirst < total && tc_tile_dead<SWAPPED>(tfirst, nsplit, m_tiles, n_tiles, MT, rows_act)) tfirst += gridDim.x;
 
     // Weights never depend on earlier kernels: the producer starts streaming the first weight tiles BEFORE the
     // programmatic-dependency wait, so the HBM latency of the weight stream hides behind the predecessor's tail.
     int pre = 0;
-    if (warp == 0 && lane == 0 && (int)blockIdx.x < total) {
+    if (warp == 0 && lane == 0 && tfirst < total) {
         int ks, mt, nt;
-        tc_tile_of<SWAPPED>(blockIdx.x, nsplit, m_tiles, n_tiles, ks, mt, nt);
+        tc_tile_of<SWAPPED>(tfirst, nsplit, m_tiles, n_tiles, ks, mt, nt);
         pre = KB < Cfg::kStages ? KB : Cfg::kStages;
         for (int kb = 0; kb < pre; ++kb) {
             mbar_expect_tx(&full[kb], Cfg::kStageBytes);
@@ -632,9 +652,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
 
     if (warp == 0) {
         if (lane == 0) {
-            if ((int)blockIdx.x < total) {
+            if (tfirst < total) {
                 int ks, mt, nt;
-                tc_tile_of<SWAPPED>(blockIdx.x, nsplit, m_tiles, n_tiles, ks, mt, nt);
+                tc_tile_of<SWAPPED>(tfirst, nsplit, m_tiles, n_tiles, ks, mt, nt);
                 for (int kb = 0; kb < pre; ++kb) {
                     if (SWAPPED) tma_load_2d(smem_w + kb * (TC_BN * TC_BK * 2), &tmW, (ks * KB + kb) * TC_BK, nt * TC_BN, &full[kb]);
                     else tma_load_2d(smem_a + kb * (MT * TC_BK * 2), &tmA, (ks * KB + kb) * TC_BK, mt * MT, &full[kb]);
@@ -645,7 +665,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
             if (!done) {
                 uint32_t stage = (pre == Cfg::kStages) ? 0 : pre, phase = (pre == Cfg::kStages) ? 1 : 0;
                 int kb0 = pre;
-                for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                for (int t = tfirst; t < total; t += gridDim.x) {
+                    if (tc_tile_dead<SWAPPED>(t, nsplit, m_tiles, n_tiles, MT, rows_act)) continue;
                     int ks, mt, nt;
                     tc_tile_of<SWAPPED>(t, nsplit, m_tiles, n_tiles, ks, mt, nt);
                     for (int kb = kb0; kb < KB; ++kb) {
@@ -668,6 +689,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
             const uint32_t idesc = (1u << 4) | ((act_f16 ? 0u : 1u) << 7) | ((act_f16 ? 0u : 1u) << 10) | ((uint32_t)(MT >> 3) << 17) | ((uint32_t)(TC_BN >> 4) << 24);
             uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                if (tc_tile_dead<SWAPPED>(t, nsplit, m_tiles, n_tiles, MT, rows_act)) continue;
                 mbar_wait(&tempty[as], aphase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * MT;
@@ -687,12 +709,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
             }
         }
     } else if (warp >= 4) {
-        if constexpr (EPI == ITB_EPI_VOCAB_K4) tc_epilogue_vocab4<MT>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane, cbuf);
-        else if constexpr (EPI == ITB_EPI_VOCAB_K8) tc_epilogue_vocab<MT, 8>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane);
-        else if constexpr (EPI == ITB_EPI_VOCAB_K16) tc_epilogue_vocab<MT, 16>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane);
-        else if constexpr (EPI == ITB_EPI_BIAS_F32) tc_epilogue<MT, EPI, float>(tmem_base, tfull, tempty, bias, reinterpret_cast<float*>(out), M, N, ldo, nsplit, part_stride, total, m_tiles, warp, lane);
-        else if (act_f16) tc_epilogue<MT, EPI, __half>(tmem_base, tfull, tempty, bias, reinterpret_cast<__half*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane);
-        else tc_epilogue<MT, EPI, __nv_bfloat16>(tmem_base, tfull, tempty, bias, reinterpret_cast<__nv_bfloat16*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane);
+        if constexpr (EPI == ITB_EPI_VOCAB_K4) tc_epilogue_vocab4<MT>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane, cbuf, 0u, rows_act);
+        else if constexpr (EPI == ITB_EPI_VOCAB_K8) tc_epilogue_vocab<MT, 8>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane, 0u, rows_act);
+        else if constexpr (EPI == ITB_EPI_VOCAB_K16) tc_epilogue_vocab<MT, 16>(tmem_base, tfull, tempty, bias, vp, M, N, total, m_tiles, n_tiles, warp, lane, 0u, rows_act);
+        else if constexpr (EPI == ITB_EPI_BIAS_F32) tc_epilogue<MT, EPI, float>(tmem_base, tfull, tempty, bias, reinterpret_cast<float*>(out), M, N, ldo, nsplit, part_stride, total, m_tiles, warp, lane, rows_act);
+        else if (act_f16) tc_epilogue<MT, EPI, __half>(tmem_base, tfull, tempty, bias, reinterpret_cast<__half*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane, rows_act);
+        else tc_epilogue<MT, EPI, __nv_bfloat16>(tmem_base, tfull, tempty, bias, reinterpret_cast<__nv_bfloat16*>(out), M, N, ldo, 1, 0, total, m_tiles, warp, lane, rows_act);
     }
 
     tc_fence_before();

@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(32 * LN_ROWS, 4) embed_ln_kernel(const ItbCtl*
     const int4 c4 = *reinterpret_cast<const int4*>(ctl);          // {step, done, steps_run, cur}
     if (c4.y != 0) return;
     const int lane = threadIdx.x & 31, r = blockIdx.x * LN_ROWS + (threadIdx.x >> 5);
-    if (r >= M) return;
+    if (r >= M || r >= itb_rows_active(ctl)) return;
     const int p = c4.x - 1;                          // 0-based position of the token consumed this step
     const int tok = tokens[((size_t)c4.w * M + r) * T_max + p];
     const int lang = tgt_lang[r / beam];
@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(32 * LN_ROWS, 4) add_ln_kernel(const ItbCtl* _
     pdl_wait();
     if (ctl != nullptr && ctl->done) return;
     const int lane = threadIdx.x & 31, r = blockIdx.x * LN_ROWS + (threadIdx.x >> 5);
-    if (r >= M) return;
+    if (r >= M || r >= itb_rows_active(ctl)) return;
     const int nv = (d + 127) / 128;
     float4 v[LN_MAXV];
 #pragma unroll
@@ -310,6 +310,7 @@ __global__ void init_state_kernel(ItbCtl* ctl, ItbGrp* grp, int* sent_done, cons
             ctl->fin_rows = 0;
             ctl->sent_done = 0;
             ctl->max_len = ml;
+            ctl->rows_active = M;
             ctl->done = all_done;
         }
     }

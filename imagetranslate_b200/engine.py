@@ -342,6 +342,11 @@ class DecodeEngine(object):
         arguments of `decode`.  Returns a list of (tokens (B_g,T_max) int32 CPU, lengths, full_lengths)."""
         lib, dev = self.lib, self.device
         G = len(groups)
+        # Row layout: groups in order of decreasing loop bound, so that the rows of groups whose search has ended form a
+        # SUFFIX of the row range -- the beam kernel publishes the live prefix (ctl.rows_active) and the GEMM / LayerNorm
+        # kernels skip the rest.  A group's arithmetic does not depend on where its rows sit; results go back in call order.
+        order = sorted(range(G), key=lambda i: (-int(groups[i]["max_len"]), i))
+        groups = [groups[i] for i in order]
         Bs = [int(g["memory"].shape[0]) for g in groups]
         Ss = [int(g["memory"].shape[1]) for g in groups]
         q = lambda v, m: -(-int(v) // m) * m
@@ -464,8 +469,8 @@ class DecodeEngine(object):
         lens = out_len[:2 * B + 8].cpu()
         self.last_steps = int(lens[2 * B + 2])
         self.launches_per_step = 2 + 11 * pw.L + ((3 + 11 * pw.L) if two else 0) + (1 if n_prop else 0)
-        res, o = [], 0
-        for Bg in Bs:
-            res.append((tok[o:o + Bg], lens[o:o + Bg], lens[B + o:B + o + Bg]))
+        res, o = [None] * G, 0
+        for gi, Bg in zip(order, Bs):
+            res[gi] = (tok[o:o + Bg], lens[o:o + Bg], lens[B + o:B + o + Bg])
             o += Bg
         return res

@@ -37,7 +37,8 @@ enum { ITB_EPI_BIAS_F32 = 0,      /* out f32  = acc + bias                      
        ITB_EPI_VOCAB_K4 = 3, ITB_EPI_VOCAB_K8 = 4, ITB_EPI_VOCAB_K16 = 5 };
 
 /* Control block living in device memory (see csrc/common.cuh for field meaning). */
-typedef struct { int step, done, steps_run, cur, fin_rows, sent_done, max_len, pad_; } itb_ctl;
+typedef struct { int step, done, steps_run, cur, fin_rows, sent_done, max_len, rows_active; } itb_ctl;   /* rows_active: rows of unfinished
+ * groups form a prefix [0, rows_active) when the groups are laid out longest loop bound first; dense kernels skip the rest */
 /* One GROUP = one reference batch (one BeamDecoder.forward call of the reference).  Several groups may be decoded
  * in lockstep as one super-batch: rows of all groups share every kernel launch (and every weight byte streamed), but
  * each group keeps the reference's per-batch loop bound and termination rule (seq_gen.py:113-117,131-136). */
