@@ -247,6 +247,10 @@ __global__ void __launch_bounds__(416, 1) attn_bulk_kernel(AttnBulkArgs a) {
     const int hoff = h * DH;
     const int koff = h * (DH * (int)sizeof(T)), voff = d * (int)sizeof(T) + koff;     // byte offsets inside a staged row
     uint32_t seq = 0, nit = 0;
+    // cross-attention: the queries of the NEXT item are requested before this item's stages are consumed (their round
+    // trip hides behind the stage loop); qn_item says which item the registers hold
+    float4 qn[4];
+    int qn_item = -1;
     for (int item = blockIdx.x; item < a.n_items; item += gridDim.x) {
         const int b = item / nz, z = item - b * nz;
         if (a.sent_done != nullptr && a.sent_done[b] != 0) continue;
@@ -266,11 +270,26 @@ __global__ void __launch_bounds__(416, 1) attn_bulk_kernel(AttnBulkArgs a) {
             ++nit;
         } else {
             const float4* qp = reinterpret_cast<const float4*>(a.q + (size_t)(row0 + min(nl, nq - 1)) * a.ldq + hoff + 16 * c);
+            if (!SELF && qn_item == item) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) qx[i] = qp[i];
+                for (int i = 0; i < 4; ++i) qx[i] = qn[i];
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) qx[i] = qp[i];
+            }
             if (SELF) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) { kx[i] = qp[d / 4 + i]; vx[i] = qp[d / 2 + i]; }
+            } else {
+                const int nx = item + (int)gridDim.x;
+                if (nx < a.n_items) {
+                    const int bn = nx / nz, zn = nx - bn * nz;
+                    const int rown = bn * a.beam + zn * 4 + min(nl, min(4, a.beam - zn * 4) - 1);
+                    const float4* qpn = reinterpret_cast<const float4*>(a.q + (size_t)rown * a.ldq + hoff + 16 * c);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) qn[i] = qpn[i];
+                    qn_item = nx;
+                }
             }
         }
         // Accumulators.  Self-attention starts them from the row's own NEW token (position pc): its K,V are in registers
