@@ -113,7 +113,7 @@ class ClockSampler(object):
 
 
 def emitted(outs):
-    return sum(int(o.numel()) - 1 for o in outs)       # language token excluded, as translate.py:55 decodes x[1:]
+    return sum(o.shape[0] for o in outs) - len(outs)   # language token excluded, as translate.py:55 decodes x[1:]
 
 
 # ------------------------------------------------------------------------------------------- reference arms (oracle port)

@@ -34,68 +34,82 @@ def shard_batches(costs: Sequence[float], world_size: int) -> List[List[int]]:
 
 class GatheredOutputs(object):
     """Result of gather_outputs on the destination rank: a read-only mapping {sentence id: 1-D LongTensor} over ONE
-    padded token matrix (rows are views; nothing is unpacked per sentence until it is asked for)."""
+    padded int32 matrix of rows [id, length, tokens...] exactly as it came off the collective.  Nothing is copied,
+    converted or indexed per sentence until it is asked for (the id index is built on first lookup)."""
 
-    def __init__(self, ids, lengths, tokens):
-        self.ids, self.lengths, self.tokens = ids, lengths, tokens          # (n,) int64, (n,) int64, (n, W) int64
-        self._row = dict(zip(ids.tolist(), range(ids.numel())))
-        self._len = lengths.tolist()
+    def __init__(self, rows):
+        self.rows = rows                                  # (n, 2 + W) int32; id = -1 marks padding rows of short shards
+        self._index = None
+
+    def _idx(self):
+        if self._index is None:
+            ids = self.rows[:, 0]
+            valid = torch.nonzero(ids >= 0).reshape(-1)
+            self._index = dict(zip(ids[valid].tolist(), valid.tolist()))
+        return self._index
+
+    @property
+    def ids(self):
+        return torch.tensor(sorted(self._idx()), dtype=torch.int64)
 
     def __len__(self):
-        return len(self._row)
+        return int((self.rows[:, 0] >= 0).sum()) if self.rows.numel() else 0
 
     def __contains__(self, i):
-        return int(i) in self._row
+        return int(i) in self._idx()
 
     def __getitem__(self, i):
-        r = self._row[int(i)]
-        return self.tokens[r, :self._len[r]]
+        r = self._idx()[int(i)]
+        return self.rows[r, 2:2 + int(self.rows[r, 1])].to(torch.int64)
 
     def keys(self):
-        return self._row.keys()
+        return self._idx().keys()
 
     def items(self):
-        return ((i, self.tokens[r, :self._len[r]]) for i, r in self._row.items())
+        return ((i, self[i]) for i in self._idx())
 
     def in_order(self):
         """Outputs sorted by sentence id (what a writer emits: the reference writes in input order, translate.py:114-120)."""
-        return [self[i] for i in sorted(self._row)]
+        return [self[i] for i in sorted(self._idx())]
 
     def emitted_tokens(self):
         """sum(len(output) - 1): the language token is not an emitted token (translate.py:55 decodes x[1:])."""
-        return int(self.lengths.sum()) - int(self.lengths.numel())
+        if not self.rows.numel():
+            return 0
+        valid = self.rows[:, 0] >= 0
+        return int(self.rows[:, 1][valid].sum()) - int(valid.sum())
 
 
 def gather_outputs(ids: Sequence[int], outputs: Sequence[torch.Tensor], device, dst: int = 0):
     """Gathers (sentence id, tokens) pairs from all ranks onto rank `dst` with ONE padded all-gather
     (NCCL over NVLink on GPUs, gloo in the CPU tests).  Returns a GatheredOutputs mapping on dst, None elsewhere.
-    Packing and unpacking are vectorised: no per-sentence Python on the send side, none on the receive side either
-    until a row is read (the row loops of round 1 cost more than the collective itself)."""
+    Packing is vectorised and the receive side is lazy: no per-sentence Python on either side of the collective
+    (the row loops of round 1 cost more than the collective itself)."""
     world = dist.get_world_size() if dist.is_initialized() else 1
     n = len(outputs)
-    lens = torch.tensor([int(o.numel()) for o in outputs], dtype=torch.int64)
-    width = int(lens.max()) if n else 0
-    ids_t = torch.as_tensor(list(ids), dtype=torch.int64)
     if n:
-        padded = torch.nn.utils.rnn.pad_sequence(list(outputs), batch_first=True, padding_value=-1).to(torch.int64)
+        padded = torch.nn.utils.rnn.pad_sequence(list(outputs), batch_first=True, padding_value=0)
+        lens = torch.tensor([o.shape[0] for o in outputs], dtype=torch.int32)
+        width = int(padded.shape[1])
     else:
-        padded = torch.zeros((0, 0), dtype=torch.int64)
-    if world == 1:
-        return GatheredOutputs(ids_t, lens, padded)
-    meta = torch.tensor([n, width], dtype=torch.int64, device=device)
-    dist.all_reduce(meta, op=dist.ReduceOp.MAX)
-    n_max, w_max = int(meta[0]), int(meta[1])
+        padded, lens, width = torch.zeros((0, 0), dtype=torch.int64), torch.zeros((0,), dtype=torch.int32), 0
+    n_max, w_max = n, width
+    if world > 1:
+        meta = torch.tensor([n, width], dtype=torch.int64, device=device)
+        dist.all_reduce(meta, op=dist.ReduceOp.MAX)
+        n_max, w_max = int(meta[0]), int(meta[1])
     # one row per sentence: [id, length, tokens...]; id = -1 marks padding rows.  Sentence ids travel as int32.
-    pack = torch.full((n_max, w_max + 2), -1, dtype=torch.int32)
-    if n:
-        pack[:n, 0], pack[:n, 1] = ids_t.to(torch.int32), lens.to(torch.int32)
-        pack[:n, 2:2 + width] = padded.to(torch.int32)
-    if torch.device(device).type == "cuda":
-        pack = pack.pin_memory().to(device, non_blocking=True)
+    pack = torch.empty((n_max, w_max + 2), dtype=torch.int32, pin_memory=(world > 1 and torch.device(device).type == "cuda"))
+    pack[:n, 0] = torch.as_tensor(list(ids), dtype=torch.int32)
+    pack[:n, 1] = lens
+    pack[:n, 2:2 + width] = padded
+    pack[:n, 2 + width:] = 0
+    pack[n:, 0] = -1
+    pack[n:, 1:] = 0
+    if world == 1:
+        return GatheredOutputs(pack)
     allp = torch.empty((world * n_max, w_max + 2), dtype=torch.int32, device=device)
-    dist.all_gather_into_tensor(allp, pack)
+    dist.all_gather_into_tensor(allp, pack.to(device, non_blocking=True))
     if dist.get_rank() != dst:
         return None
-    allp = allp.cpu()
-    allp = allp[allp[:, 0] >= 0]
-    return GatheredOutputs(allp[:, 0].to(torch.int64), allp[:, 1].to(torch.int64), allp[:, 2:].to(torch.int64))
+    return GatheredOutputs(allp.cpu())
