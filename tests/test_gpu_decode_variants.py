@@ -159,3 +159,53 @@ def test_translate_img_chain_of_image_embed_calls():
     with torch.no_grad():
         got = chain(lambda **kw: bd(**kw))
     assert got == want
+
+
+def test_forward_many_packs_the_variants():
+    """forward_many with variant batches: proposal batches of different widths must not share a super-batch (PAD proposals
+    are attended, so padding a narrower list would change its sentences), object-stream batches may (both memories travel
+    per group); every batch must come out as its own forward call gives it."""
+    V, beam = 900, 3
+    tp = R.FakeTextProcessor(V)
+    torch.manual_seed(91)
+    model = R.Seq2SeqModel(tp, lang_dec=False, tie_embed=False, enc_layer=1, dec_layer=2, use_proposals=True).eval()
+    with torch.no_grad():
+        model.lexical_gate.normal_()
+        model.output_layer[1].layer.bias[4] += 0.8
+    model = model.to(DEV)
+    batches = []
+    for i, (B, S, P) in enumerate([(4, 9, 5), (3, 10, 5), (5, 11, 3), (2, 12, 3), (6, 9, 7)]):
+        src, mask, pad_idx = cases.make_text_batch(B, S, V, 400 + i)
+        prop = torch.randint(7, V, (B, P), generator=torch.Generator().manual_seed(500 + i))
+        prop[0, P // 2:] = 0
+        batches.append(dict(src_inputs=src, src_mask=mask, src_sizes=pad_idx, src_langs=torch.zeros(B, dtype=torch.long),
+                            first_tokens=torch.full((B,), 6), tgt_langs=torch.ones(B, dtype=torch.long), pad_idx=0, proposals=prop))
+    bd = BeamDecoder(model, beam_width=beam, dtype="fp32", **cases.GEN)
+    assert [len(p) for p in bd._pack(batches, 4096)] == [2, 2, 1]
+    with torch.no_grad():
+        seq = [bd(**kw) for kw in batches]
+        par = bd.forward_many(batches, lanes=2, rows=4096)
+    assert [[o.tolist() for o in b] for b in par] == [[o.tolist() for o in b] for b in seq]
+    cpu = model.cpu()
+    want = R.beam_search(cpu, beam_width=beam, **cases.GEN, **batches[2])
+    assert [o.tolist() for o in seq[2]] == [w.tolist() for w in want]
+    # object stream: two batches with different object counts in one super-batch
+    m2, kw_a, c = cases.build("image_obj_stream")
+    kw_a = dict(kw_a); kw_a.pop("beam_width")
+    mem, obj = m2.encode(images=kw_a["images"])
+    kw_b = dict(kw_a, first_tokens=kw_a["first_tokens"][:2], tgt_langs=kw_a["tgt_langs"][:2], images=torch.ones(2, 1))
+
+    class TwoBatches(object):          # hands out the memories of batch a (zeros image) or b (ones image: fewer objects)
+        def __call__(self, src_inputs=None, src_mask=None, src_langs=None, images=None):
+            if float(images.flatten()[0]) == 0.0:
+                return mem.to(images.device), obj.to(images.device)
+            return mem[:2].flip(0).contiguous().to(images.device), obj[:2, :4].contiguous().to(images.device)
+
+    m2.encode = TwoBatches()
+    m2 = m2.to(DEV)
+    bd2 = BeamDecoder(m2, beam_width=4, dtype="fp32", **cases.GEN)
+    with torch.no_grad():
+        seq2 = [bd2(**kw_a), bd2(**kw_b)]
+        par2 = bd2.forward_many([kw_a, kw_b], lanes=1, rows=4096)
+    assert [len(p) for p in bd2._pack([kw_a, kw_b], 4096)] == [2]
+    assert [[o.tolist() for o in b] for b in par2] == [[o.tolist() for o in b] for b in seq2]
