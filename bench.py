@@ -48,7 +48,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the per-batch / GPU-eager / extra roofline legs")
     ap.add_argument("--cpu-sentences", type=int, default=12)
-    ap.add_argument("--eos-bias", type=float, default=0.0, help="added to the EOS logit bias: > 0 makes hypotheses finish early (random-init weights never emit EOS on their own, so the default workload runs every sentence to its max_len)")
+    ap.add_argument("--eos-bias", type=float, default=0.0, help="added to the EOS logit bias: 1.5-2.5 makes a share of the hypotheses finish early (random-init weights never emit EOS on their own, so the default workload runs every sentence to its max_len; 6 ends every sentence at step 1)")
     ap.add_argument("--cpu-full", action="store_true", help="cpu baseline on the FULL median batch (minutes)")
     ap.add_argument("--single-leg", action="store_true", help="time ONE leg only, from pinned host inputs (value = e2e); for the long config-5 passes")
     ap.add_argument("--no-gather", action="store_true", help="diagnostic: leave the NCCL output gather out of the passes (N > 1)")
