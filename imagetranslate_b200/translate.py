@@ -46,7 +46,7 @@ def get_lm_option_parser():
     # additions of this driver (defaults keep the reference's results)
     parser.add_option("--rows", dest="rows", help="beam rows per super-batch", type="int", default=4096)
     parser.add_option("--lanes", dest="lanes", help="super-batches in flight per GPU", type="int", default=3)
-    parser.add_option("--window", dest="window", help="batches handed to the decoder at once", type="int", default=96)
+    parser.add_option("--window", dest="window", help="batches handed to the decoder at once", type="int", default=256)
     return parser
 
 

@@ -28,7 +28,7 @@ GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "confi
 def _options(**kw):
     base = dict(input_path=None, src_lang="fa", target_lang="en", output_path=None, batch=4000, tokenizer_path=GOLD, cache_size=300,
                 model_path=None, verbose=False, beam_width=4, max_len_a=1.3, max_len_b=5, len_penalty_ratio=0.8, total_capacity=600,
-                fp16=False, rows=4096, lanes=2, window=96)
+                fp16=False, rows=4096, lanes=3, window=256)
     base.update(kw)
     return types.SimpleNamespace(**base)
 
