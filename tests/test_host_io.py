@@ -211,3 +211,24 @@ def test_product_seq2seq_and_mass_share_the_decode_surface():
     tp = SyntheticTextProcessor(100)
     m = MassSeq2Seq(tp, lang_dec=False, **SMALL)
     assert isinstance(m, Seq2Seq) and m.decoder.decoder.layer[0].attention is m.encoder.encoder.layer[0].attention
+
+
+@needs_ref
+def test_get_outputs_until_eos_equals_the_reference():
+    """src/seq_gen.py:6-24: cut before the first EOS, else at size_limit[r] (or the row length); remove_first_token."""
+    from imagetranslate_b200.seq_gen import get_outputs_until_eos
+    ns = reference_loader.load()
+    g = torch.Generator().manual_seed(5)
+    out = torch.randint(5, 12, (9, 14), generator=g)
+    out[2, 3] = 4
+    out[2, 7] = 4
+    out[5, 0] = 4
+    out[7, 13] = 4
+    lim = torch.randint(1, 15, (9,), generator=g)
+    for kw in (dict(), dict(size_limit=lim), dict(size_limit=lim, remove_first_token=True), dict(remove_first_token=True)):
+        a = ns.seq_gen.get_outputs_until_eos(4, out, **kw)
+        b = get_outputs_until_eos(4, out, **kw)
+        assert [x.tolist() for x in a] == [x.tolist() for x in b], kw
+    a = ns.seq_gen.get_outputs_until_eos(4, out[2])
+    b = get_outputs_until_eos(4, out[2])
+    assert [x.tolist() for x in a] == [x.tolist() for x in b]

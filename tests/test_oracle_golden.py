@@ -67,3 +67,37 @@ def test_restated_per_step_log_probs_match_the_recorded_reference_run():
         pre = t["prefixes"].reshape(-1, t["prefixes"].shape[-1])
         assert pre.tolist() == z["step_prefixes"][k, :, :pre.shape[1]].tolist()
         assert float((t["scores"].reshape(-1) - torch.from_numpy(z["step_scores"][k])).abs().max()) < 2e-5
+
+
+def test_search_step_semantics_by_hand():
+    """Hand-checkable trace of reference src/seq_gen.py:194-227 on a scripted 6-token vocabulary,
+    one sentence, beam 2, eos = 4, pad = 0, alpha = 0.8: slot 0 already holds EOS, slot 1 is live.
+      * the finished row is zeroed: its 6 candidates tie at s0 / lp(n0), an IMPROVED score (the score is re-divided);
+      * top-2 therefore takes two of those tied candidates (which two is torch.topk's business);
+      * new slot 0 is rewritten to PAD because OLD slot 0 had EOS (indexed by new slot, old flag) -> back-pointer 0, token PAD;
+        new slot 1 is NOT rewritten (old slot 1 was live) although it also descends from the finished row: it keeps the
+        tie-chosen token -- the cloning of Appendix B.3;
+      * sizes count non-PAD tokens; scores are the un-rewritten top-k values."""
+    import math
+    V, beam, eos, pad, alpha = 6, 2, 4, 0, 0.8
+    prefixes = torch.tensor([[[5, 3, 4], [5, 2, 1]]])              # (B=1, beam, i=3): slot 0 = "3 </s>", slot 1 = "2 1"
+    scores = torch.tensor([[-1.2, -1.5]])
+    sizes = torch.tensor([[2.0, 2.0]])
+    logp = torch.log_softmax(torch.tensor([[0.0, 0.1, 0.2, 0.3, 0.4, 0.5], [0.0, 2.0, 0.0, 0.0, 0.0, 0.0]]), -1)
+    new_p, new_s, new_n, raw = R.search_step(3, logp, prefixes, scores, sizes, torch.tensor([50]), eos, pad, beam, alpha)
+    lp = ((2.0 + 6.0) / 6.0) ** alpha
+    tied = -1.2 / lp                                               # every continuation of the finished row
+    best_live = (-1.5 + float(logp[1, 1])) / lp
+    assert tied > best_live                                        # the finished row outranks the live one
+    assert torch.allclose(new_s, torch.tensor([[tied, tied]]), atol=1e-6)
+    assert (raw // V).tolist() == [[0, 0]]                         # both winners descend from the finished row
+    assert new_p[0, 0].tolist() == [5, 3, 4, pad]                  # forced PAD on new slot 0 (old slot 0 had EOS)
+    assert new_p[0, 1].tolist()[:3] == [5, 3, 4]                   # clone of the finished hypothesis ...
+    assert new_p[0, 1, 3].item() == int(raw[0, 1]) % V             # ... with a tie-chosen token, NOT rewritten
+    assert new_n[0, 0].item() == 2.0                               # PAD does not count
+    assert new_n[0, 1].item() == 2.0 + float(int(raw[0, 1]) % V != pad)
+    # over-length sentence (max_lens < i + 1): every new slot is rewritten to old slot 0 + PAD (:207)
+    p2, s2, n2, _ = R.search_step(3, logp, torch.tensor([[[5, 3, 2], [5, 2, 1]]]), scores, sizes, torch.tensor([3]), eos, pad, beam, alpha)
+    assert p2[0].tolist() == [[5, 3, 2, pad], [5, 3, 2, pad]]
+    assert torch.allclose(s2, torch.tensor([[-1.2 / lp, -1.2 / lp]]), atol=1e-6) and n2.tolist() == [[2.0, 2.0]]
+    assert math.isclose(lp, float(R.len_penalty(torch.tensor([2.0]), alpha)[0, 0]), rel_tol=1e-6)
