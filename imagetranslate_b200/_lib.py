@@ -78,6 +78,8 @@ _SIGS = {
     "itb_decoder_capture": (C.c_int, [P, C.c_int]),
     "itb_decoder_launch": (C.c_int, [P, P]),
     "itb_cross_kv": (C.c_int, [C.c_int, C.c_int, P, P, P, P, C.c_int, C.c_int, C.c_int, P]),
+    "itb_linear_add_ln_static": (C.c_int, [C.c_int, C.c_int, P, P, P, P, P, C.c_float, P, P, C.c_int, C.c_int, C.c_int, P]),
+    "itb_static_scratch_floats": (C.c_int, []),
 }
 EXPORTS = tuple(sorted(_SIGS))
 _lib = None

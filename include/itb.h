@@ -22,6 +22,8 @@ extern "C" {
 #endif
 
 #define ITB_ABI_VERSION 4
+#define ITB_STATIC_SCRATCH_FLOATS (2 * 1024 * 1024)   /* floats of the library's file-scope device scratch (8 MiB per GPU):
+                                                       * itb_linear_add_ln_static accepts M * d <= this / ITB_Y_PARTIALS */
 #define ITB_Y_PARTIALS 4   /* cfg.y holds up to this many split-K partial outputs: [ITB_Y_PARTIALS][M][d] floats */
 /* dtype codes: (linear-weight type, activation / KV-cache type).  Accumulation, softmax, LayerNorm statistics,
  * logits and beam scores are always fp32. */
@@ -223,6 +225,21 @@ int itb_decoder_launch(itb_decoder* dec, void* stream);
  * key/value on encoder_hidden_states; the reference redoes it every step: SURVEY K5). */
 int itb_cross_kv(int dtype, int impl, const void* memory, const void* w_ckv, const float* b_ckv, void* cross_kv,
                  int rows, int d, int L, void* stream);
+
+
+/* -------- allocation-free variant -------- */
+/* x = LayerNorm(A[M][K] . W[d][K]^T + bias + x), in place on x_f32 with its act copy: itb_linear (f32 epilogue, the decode
+ * path's split-K plan) followed by itb_add_ln, with the split-K partial outputs held in a file-scope device array of the
+ * library instead of a caller-allocated buffer.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  Allocates nothing (no cudaMalloc / cudaFree / allocating library call).  Limit: M * d <=
+ * ITB_STATIC_SCRATCH_FLOATS / ITB_Y_PARTIALS = 524288 (682 rows at d = 768); larger problems are rejected with -2 and a
+ * message in itb_last_error().  The array (8 MiB) is held by every GPU that loads the library until the process exits and is
+ * shared by every call on that GPU: calls that overlap on the GPU race on it (calls on one stream are ordered).  It keeps
+ * the last call's partials; nothing in it needs to start at zero (the GEMM overwrites all that add_ln reads). */
+int itb_linear_add_ln_static(int dtype, int impl, const void* A, const void* W, const float* bias, const float* g,
+                             const float* b, float eps, float* x_f32, void* x_act, int M, int d, int K, void* stream);
+int itb_static_scratch_floats(void);   /* ITB_STATIC_SCRATCH_FLOATS of the loaded library */
 
 #ifdef __cplusplus
 }
