@@ -46,8 +46,29 @@ __device__ __forceinline__ int itb_rows_active(const ItbCtl* ctl) {
     return ra > 0 ? ra : 0x7fffffff;
 }
 
+#ifndef ITB_TIMELINE
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#else
+// Diagnostic build (csrc/timeline_all.cu, never the shipped library): thread 0 of block 0 of every kernel stamps
+// %globaltimer when it enters the kernel (at pdl_trigger) and when its programmatic dependency resolves (after pdl_wait), so
+// that the chain of a real search step can be laid out launch by launch.  Entry = (source tag, time); tag = file * 100000 +
+// line (+ 50000 for the dependency stamp).
+#define ITB_TL_CAP 16384
+__device__ unsigned long long g_itb_tl[1 + 2 * ITB_TL_CAP];
+__device__ __forceinline__ void itb_tl_stamp(int tag) {
+    if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        const unsigned long long i = atomicAdd(&g_itb_tl[0], 1ull);
+        if (i < ITB_TL_CAP) { g_itb_tl[1 + 2 * i] = (unsigned long long)tag; g_itb_tl[2 + 2 * i] = t; }
+    }
+}
+__device__ __forceinline__ void pdl_wait_impl() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger_impl() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#define pdl_wait() do { pdl_wait_impl(); itb_tl_stamp(ITB_TL_FILE * 100000 + 50000 + __LINE__); } while (0)
+#define pdl_trigger() do { itb_tl_stamp(ITB_TL_FILE * 100000 + __LINE__); pdl_trigger_impl(); } while (0)
+#endif
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

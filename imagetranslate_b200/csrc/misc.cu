@@ -1,5 +1,6 @@
 // Embedding + LayerNorm, residual + LayerNorm, state init, output extraction.
 // HBM-bound row kernels: one CTA per row, float4 accesses, fp32 statistics.
+#include <stdlib.h>
 #include "common.cuh"
 #include "launch.h"
 
@@ -144,6 +145,97 @@ __global__ void __launch_bounds__(32 * LN_ROWS, 4) add_ln_kernel(const ItbCtl* _
         }
     }
     ln_row_write<TA>(v, nv, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, lane);
+}
+
+// The same kernel for d = 128 * NV known at compile time, written for memory-level parallelism: the generic kernel above
+// walks its float4 columns under run-time guards, so every load waits for the one before it (6 x (partials + 1) dependent
+// round trips per row: ~10 us per launch at ANY row count, 30 % of a small batch's search step).  Here the row's first
+// partial, its residual and the control block are requested together, the remaining partials two at a time, and the
+// termination / dead-row test (which only has to precede the stores) waits for nothing else.  Same summation order.
+// ld.volatile: nvcc AND ptxas keep these loads where they are written, i.e. ahead of the early-exit tests that follow them (ptxas
+// would otherwise hoist the tests, and with them the control block's round trip, in front of the row's loads)
+__device__ __forceinline__ float4 ld_f4_now(const float* p) {
+    float4 v;
+    asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ int4 ld_i4_now(const void* p) {
+    int4 v;
+    asm volatile("ld.volatile.global.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+
+template <typename TA, int NV>
+__global__ void __launch_bounds__(32 * LN_ROWS, 2) add_ln_fast_kernel(const ItbCtl* __restrict__ ctl, const float* __restrict__ y,
+                                                          int n_partial, const float* __restrict__ g,
+                                                          const float* __restrict__ b, float eps, float* __restrict__ x_f32,
+                                                          TA* __restrict__ x_act, int M) {
+    pdl_trigger();
+    pdl_wait();
+    constexpr int d = 128 * NV;
+    const int lane = threadIdx.x & 31, r = blockIdx.x * LN_ROWS + (threadIdx.x >> 5);
+    if (r >= M) return;
+    int4 c0 = make_int4(0, 0, 0, 0), c1 = make_int4(0, 0, 0, 0);
+    if (ctl != nullptr) {
+        c0 = ld_i4_now(ctl);                                       // {step, done, steps_run, cur}
+        c1 = ld_i4_now(reinterpret_cast<const int4*>(ctl) + 1);    // {fin_rows, sent_done, max_len, rows_active}
+    }
+    const float* yr = y + (size_t)r * d + lane * 4;
+    float* xr = x_f32 + (size_t)r * d + lane * 4;
+    float4 a[NV], xv[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) a[i] = ld_f4_now(yr + i * 128);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) xv[i] = ld_f4_now(xr + i * 128);
+    if (c0.y != 0 || (c1.w > 0 && r >= c1.w)) return;            // search over / row of a finished group (itb_rows_active)
+    const size_t ps = (size_t)M * d;
+    int sp = 1;
+    for (; sp + 1 < n_partial; sp += 2) {
+        float4 t0[NV], t1[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) t0[i] = *reinterpret_cast<const float4*>(yr + sp * ps + i * 128);
+#pragma unroll
+        for (int i = 0; i < NV; ++i) t1[i] = *reinterpret_cast<const float4*>(yr + (sp + 1) * ps + i * 128);
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            a[i].x += t0[i].x; a[i].y += t0[i].y; a[i].z += t0[i].z; a[i].w += t0[i].w;
+            a[i].x += t1[i].x; a[i].y += t1[i].y; a[i].z += t1[i].z; a[i].w += t1[i].w;
+        }
+    }
+    if (sp < n_partial) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const float4 t = *reinterpret_cast<const float4*>(yr + sp * ps + i * 128);
+            a[i].x += t.x; a[i].y += t.y; a[i].z += t.z; a[i].w += t.w;
+        }
+    }
+    // LayerNorm as ln_row_write (two-pass statistics, same expression order), all NV columns live
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        a[i] = make_float4(a[i].x + xv[i].x, a[i].y + xv[i].y, a[i].z + xv[i].z, a[i].w + xv[i].w);
+        s += (a[i].x + a[i].y) + (a[i].z + a[i].w);
+    }
+    const float mean = warp_sum(s) / (float)d;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const float a0 = a[i].x - mean, a1 = a[i].y - mean, a2 = a[i].z - mean, a3 = a[i].w - mean;
+        q += (a0 * a0 + a1 * a1) + (a2 * a2 + a3 * a3);
+    }
+    const float rstd = rsqrtf(warp_sum(q) / (float)d + eps);
+    TA* ar = x_act + (size_t)r * d + lane * 4;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const float4 gg = *reinterpret_cast<const float4*>(g + lane * 4 + i * 128), bb = *reinterpret_cast<const float4*>(b + lane * 4 + i * 128);
+        float4 o;
+        o.x = (a[i].x - mean) * rstd * gg.x + bb.x;
+        o.y = (a[i].y - mean) * rstd * gg.y + bb.y;
+        o.z = (a[i].z - mean) * rstd * gg.z + bb.z;
+        o.w = (a[i].w - mean) * rstd * gg.w + bb.w;
+        *reinterpret_cast<float4*>(xr + i * 128) = o;
+        store4(ar + i * 128, o);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -391,7 +483,20 @@ int itb_add_ln(int dtype, const itb_ctl* ctl, const float* y, int n_partial, con
     cudaStream_t s = (cudaStream_t)stream;
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
     cudaError_t e;
-    if (dtype == ITB_BF16)
+    static int fast = -1;                        // ITB_LN_FAST=0: the generic kernel at every width (A/B timing)
+    if (fast < 0) {
+        const char* ev = getenv("ITB_LN_FAST");
+        fast = (ev != nullptr && ev[0] == '0') ? 0 : 1;
+    }
+    if (fast != 0 && d == 768) {
+        if (dtype == ITB_BF16)
+            e = itb_launch(add_ln_fast_kernel<__nv_bfloat16, 6>, lgrid, lblock, smem, s, c, y, n_partial, g, b, eps, x_f32,
+                           (__nv_bfloat16*)x_act, M);
+        else if (dtype == ITB_F16)
+            e = itb_launch(add_ln_fast_kernel<__half, 6>, lgrid, lblock, smem, s, c, y, n_partial, g, b, eps, x_f32, (__half*)x_act, M);
+        else
+            e = itb_launch(add_ln_fast_kernel<float, 6>, lgrid, lblock, smem, s, c, y, n_partial, g, b, eps, x_f32, (float*)x_act, M);
+    } else if (dtype == ITB_BF16)
         e = itb_launch(add_ln_kernel<__nv_bfloat16>, lgrid, lblock, smem, s, c, y, n_partial, g, b, eps, x_f32,
                        (__nv_bfloat16*)x_act, M, d);
     else if (dtype == ITB_F16)
