@@ -47,12 +47,18 @@ struct AttnMmaArgs {
     int M, beam, d, T_max, S, L, layer, n_warps;
 };
 
-template <typename T, bool SELF, int STAGE>
+// SPLIT (small launches, where a step is bound by the length of one warp's walk and most SMs idle): the AM_WARPS warps of
+// a CTA share ONE item; warp w walks stages w, w + AM_WARPS, ... of the virtual position list and the partial softmax
+// states (max, sum, unnormalised output) are merged through shared memory by warp 0 (split-K for attention).
+template <typename T, bool SELF, int STAGE, bool SPLIT = false>
 __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(AttnMmaArgs a) {
     pdl_trigger();
     const int lane = threadIdx.x & 31, nl = lane >> 2, c = lane & 3;       // nl: B-fragment column / C row; c: quad lane
-    const int wg = blockIdx.x * AM_WARPS + (threadIdx.x >> 5);
-    if (wg >= a.n_warps) return;
+    const int wsub = SPLIT ? (int)(threadIdx.x >> 5) : 0;                  // SPLIT: this warp's share of the stages
+    constexpr int NSPLIT = SPLIT ? AM_WARPS : 1;
+    const int sb0 = wsub * STAGE;                                          // first virtual position of this warp's first stage
+    const int wg = SPLIT ? (int)blockIdx.x : (int)(blockIdx.x * AM_WARPS + (threadIdx.x >> 5));
+    if (wg >= a.n_warps) return;                                           // SPLIT: uniform over the CTA
     const int d = a.d, H = d / DH, nz = (a.beam + 3) >> 2;
     const int h = wg % H, z = (wg / H) % nz, b = wg / (H * nz);
     const int q0 = z * 4, row0 = b * a.beam + q0, nq = min(4, a.beam - q0);
@@ -82,7 +88,7 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
         for (int kv = 0; kv < 2; ++kv) {                              // group 0: K halves, group 1: V halves
 #pragma unroll
             for (int k = 0; k < STAGE / 4; ++k) {
-                const int row = 4 * k + rsub;
+                const int row = sb0 + 4 * k + rsub;
                 if ((row & ~31) < a.S) {
                     const bool ok = row < a.S;
                     const T* src = cbase + (ok ? (size_t)row * cstride + (size_t)kv * d + piece * 8 : (size_t)0);
@@ -94,7 +100,7 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
         }
 #pragma unroll
         for (int hv = 0; hv < AM_NCH; ++hv) {
-            const int v = 32 * hv + lane;
+            const int v = sb0 + 32 * hv + lane;
             mk0[hv] = (a.mask != nullptr && v < a.S) ? (int)a.mask[(size_t)b * a.S + v] : 1;
         }
         if (a.early_kv != 0) pdl_wait();
@@ -159,7 +165,7 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
         pos_stride = (size_t)2 * d;
         anc0 = a.anc + ((size_t)c4.w * a.M + row0) * a.T_max;
         // append the new K,V of the group's rows at position pc: lane (nl < nq, c) owns dims [16c,16c+16) of row nl
-        if (nl < nq) {
+        if (nl < nq && wsub == 0) {
             T* dst = reinterpret_cast<T*>(a.kv) + ((size_t)(row0 + nl) * a.T_max + pc) * pos_stride + hoff + 16 * c;
             uint32_t w[8];
 #pragma unroll
@@ -193,7 +199,8 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
         }
         tl = pc - cshared + 1;
         nv = cshared + nq * tl;
-        __syncwarp();                    // the appended rows are read back below by other lanes of this warp
+        if (SPLIT) __syncthreads();      // the appended rows are read back below by other lanes of this warp (SPLIT: CTA)
+        else __syncwarp();
     } else {
         base = reinterpret_cast<const T*>(a.kv) + ((size_t)b * a.S * a.L + a.layer) * 2 * d + hoff;
         pos_stride = (size_t)a.L * 2 * d;
@@ -233,7 +240,7 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
                 if (in) { rowidx[hv] = (uint32_t)((b * a.beam + slot) * a.T_max + p) * stride16; meta[hv] = tail ? (1 << qi) : 0xF; }
             } else if (v < nv) {
                 rowidx[hv] = (uint32_t)v * stride16;
-                const int mk = (sb == 0) ? mk0[hv] : ((mrow != nullptr) ? (int)mrow[v] : 1);
+                const int mk = (sb == sb0) ? mk0[hv] : ((mrow != nullptr) ? (int)mrow[v] : 1);
                 meta[hv] = 0xF | ((mk == 0) ? 0x10 : 0);
             }
         }
@@ -258,17 +265,18 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
     //      copies in flight while it computes.  The position list of stage s+1 is built at the top of stage s. ----
     uint32_t rowidx[AM_NCH], rowidx_n[AM_NCH];
     int meta[AM_NCH], meta_n[AM_NCH];
-    build_list(0, rowidx, meta);
-    if (SELF) {                                                       // cross: stage 0 was requested at the top
-        const int nch0 = min(AM_NCH, (nv + 31) >> 5);
+    constexpr int STEP = NSPLIT * STAGE;                             // distance between two stages of one warp
+    build_list(sb0, rowidx, meta);
+    if (SELF) {                                                       // cross: this warp's first stage was requested at the top
+        const int nch0 = min(AM_NCH, (nv - sb0 + 31) >> 5);          // <= 0: this warp has no stage (nothing is copied)
         issue_half(rowidx, nch0, 0);
         issue_half(rowidx, nch0, 1);
     }
-    for (int sb = 0; sb < nv; sb += STAGE) {
+    for (int sb = sb0; sb < nv; sb += STEP) {
         const int nchunk = min(AM_NCH, (nv - sb + 31) >> 5);         // 32-position chunks in this stage (warp-uniform)
-        const bool has_next = sb + STAGE < nv;
-        const int nchunk_n = min(AM_NCH, (nv - sb - STAGE + 31) >> 5);
-        if (has_next) build_list(sb + STAGE, rowidx_n, meta_n);
+        const bool has_next = sb + STEP < nv;
+        const int nchunk_n = min(AM_NCH, (nv - sb - STEP + 31) >> 5);
+        if (has_next) build_list(sb + STEP, rowidx_n, meta_n);
         asm volatile("cp.async.wait_group 1;" ::: "memory");        // K of this stage has landed (V may still be in flight)
         __syncwarp();
         bool k_next = false;
@@ -363,13 +371,47 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
     // ---- normalise and store: lane (nl < nq, c) holds dims [16c,16c+16) of row nl ----
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+    // this lane's 16 output dims, unnormalised (hi + lo accumulator rows): f[i] / f[4 + i] pair up as in the stores below
+    float f[16];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        f[2 * i] = o[2 * i][0] + o[2 * i][2];     f[2 * i + 1] = o[2 * i + 1][0] + o[2 * i + 1][2];
+        f[8 + 2 * i] = o[2 * i][1] + o[2 * i][3]; f[8 + 2 * i + 1] = o[2 * i + 1][1] + o[2 * i + 1][3];
+    }
+    if (SPLIT) {
+        // every warp publishes {m, l, f[16]} of its lanes in its own (now idle) staging buffer; warp 0 merges
+        __syncwarp();
+        float* mine = reinterpret_cast<float*>(ws) + lane * 18;
+        mine[0] = m_run; mine[1] = l_run;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) mine[2 + i] = f[i];
+        __syncthreads();
+        if (wsub != 0) return;
+        float mm = m_run;
+#pragma unroll
+        for (int w2 = 1; w2 < NSPLIT; ++w2)
+            mm = fmaxf(mm, reinterpret_cast<const float*>(am_smem + (size_t)w2 * (STAGE * AM_ROWB))[lane * 18]);
+        const float mu = (mm == -INFINITY) ? 0.f : mm;
+        const float c0s = __expf(m_run - mu);                             // -inf -> 0: a warp that saw nothing visible
+        l_run *= c0s;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) f[i] *= c0s;
+#pragma unroll
+        for (int w2 = 1; w2 < NSPLIT; ++w2) {
+            const float* oth = reinterpret_cast<const float*>(am_smem + (size_t)w2 * (STAGE * AM_ROWB)) + lane * 18;
+            const float cs = __expf(oth[0] - mu);
+            l_run += oth[1] * cs;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) f[i] += oth[2 + i] * cs;
+        }
+    }
     if (nl < nq) {
         const float inv = 1.0f / l_run;
         uint32_t w[8];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            w[i] = Mma16<T>::pack((o[2 * i][0] + o[2 * i][2]) * inv, (o[2 * i + 1][0] + o[2 * i + 1][2]) * inv);
-            w[4 + i] = Mma16<T>::pack((o[2 * i][1] + o[2 * i][3]) * inv, (o[2 * i + 1][1] + o[2 * i + 1][3]) * inv);
+            w[i] = Mma16<T>::pack(f[2 * i] * inv, f[2 * i + 1] * inv);
+            w[4 + i] = Mma16<T>::pack(f[8 + 2 * i] * inv, f[8 + 2 * i + 1] * inv);
         }
         uint4* dp = reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.ctx) + (size_t)(row0 + nl) * d + hoff + 16 * c);
         dp[0] = make_uint4(w[0], w[1], w[2], w[3]);
@@ -392,10 +434,35 @@ static int launch_attn_mma_stage(const AttnMmaArgs& a, bool self, cudaStream_t s
     return itb_check_launch(self ? "self_attention" : "cross_attention");
 }
 
+// SPLIT launch: one CTA per item, its four warps sharing the item's stages
+template <typename T>
+static int launch_attn_mma_split(const AttnMmaArgs& a, bool self, cudaStream_t s) {
+    const dim3 grid(a.n_warps), block(AM_THREADS);
+    static bool attr_self[ITB_MAX_DEVICES] = {}, attr_cross[ITB_MAX_DEVICES] = {};
+    {
+        cudaError_t e1 = itb_smem_attr_once(attr_self, attn_mma_kernel<T, true, 64, true>, AM_SMEM(64));
+        cudaError_t e2 = itb_smem_attr_once(attr_cross, attn_mma_kernel<T, false, 64, true>, AM_SMEM(64));
+        if (e1 != cudaSuccess || e2 != cudaSuccess) { itb_set_error("attention: cudaFuncSetAttribute failed"); return -1; }
+    }
+    cudaError_t e = self ? itb_launch(attn_mma_kernel<T, true, 64, true>, grid, block, (size_t)AM_SMEM(64), s, a)
+                         : itb_launch(attn_mma_kernel<T, false, 64, true>, grid, block, (size_t)AM_SMEM(64), s, a);
+    if (e != cudaSuccess) { itb_set_error("%s: launch failed: %s", self ? "self_attention" : "cross_attention", cudaGetErrorString(e)); return -1; }
+    return itb_check_launch(self ? "self_attention" : "cross_attention");
+}
+
 template <typename T>
 static int launch_attn_mma(AttnMmaArgs a, bool self, cudaStream_t s) {
     const int B = a.M / a.beam, H = a.d / DH;
     a.n_warps = B * H * ((a.beam + 3) / 4);
+    // Small launches (at most two waves of one-item CTAs, 3 CTAs per SM): the step waits for the longest walk of a single
+    // warp while most of the GPU idles, so the item's stages are shared by the four warps of a CTA.
+    // ITB_ATTN_SPLIT = item count up to which this applies (0: never).
+    static int split_max = -1;
+    if (split_max < 0) {
+        const char* e = getenv("ITB_ATTN_SPLIT");
+        split_max = (e != nullptr) ? atoi(e) : 2 * 3 * itb_num_sms();
+    }
+    if (a.n_warps <= split_max) return launch_attn_mma_split<T>(a, self, s);
     // more than ~2 waves of the 3-CTA build (148 SMs x 12 warps): occupancy beats round trips (measured at 4096 rows:
     // step -28 us; at 244 rows the 64-position build is 25 us per step faster)
     static int forced = -1;

@@ -210,6 +210,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     }
 
     // ---------------------------------- phase 2 (one CTA per sentence) ----------------------------------
+    ITB_TL(1);
     if (!gdone) {
     const int nrows = first ? 1 : K;
     float* rc_val = s_val;      // [nrows][K] row candidates (sentence-level values)
@@ -291,11 +292,13 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
 #pragma unroll
                 for (int j = 0; j < CPL; ++j) mm = fmaxf(mm, cmr[j]);
                 mm = warp_max(mm);
+                ITB_TL(10);
 #pragma unroll
                 for (int j = 0; j < CPL; ++j)
                     if (cmr[j] != -INFINITY) ss += csr[j] * expf(cmr[j] - mm);        // same order as the looped form
                 ss = warp_sum(ss);
                 logz = logf(ss);
+                ITB_TL(11);
                 // T = K-th largest chunk maximum (a real logit each): a lower bound of the row's K-th largest logit, so
                 // only chunks whose maximum reaches T can hold a top-K entry -- typically K..2K of them
                 float tl = -INFINITY, T = -INFINITY;
@@ -317,6 +320,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
                         }
                     }
                 }
+                ITB_TL(12);
                 // queue the qualifying chunks (compacted over the warp), insert them 32 at a time
                 int cnt = 0;
 #pragma unroll
@@ -338,7 +342,9 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
                     }
                 }
                 __syncwarp();
+                ITB_TL(13);
                 if (cnt > 0) insert_chunks(cnt);
+                ITB_TL(14);
             } else {
                 mm = -INFINITY;
                 for (int ci = lane; ci < nc; ci += 32) mm = fmaxf(mm, __ldcg(cmp + ci));
@@ -427,6 +433,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
         }
     }
     __syncthreads();
+    ITB_TL(2);
     if (w == 0) {
         warp_select(rc_val, rc_idx, nrows * K, K, s_top_val, s_top_idx, lane);              // :203
         if (lane < K) {
@@ -447,6 +454,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
         }
     }
     __syncthreads();
+    ITB_TL(3);
     // new prefixes (:217-224) and ancestor table (replaces the KV gather)
     for (int j = 0; j < K; ++j) {
         const int src = s_src[j];
@@ -462,6 +470,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     }
     }   // !gdone
     __syncthreads();
+    ITB_TL(4);
     if (tid == 0) {
         a.sent_counter[b] = 0;
         __threadfence();
@@ -471,6 +480,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
     }
     __syncthreads();
     if (!s_last) return;
+    ITB_TL_ANY(5);
     // ---- the last sentence of the step: per-group termination (seq_gen.py:131,134), then advance the step ----
     __shared__ int s_all_done;
     if (tid == 0) s_all_done = 1;
@@ -502,6 +512,7 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
         ctl->sent_done = 0;
         ctl->done = s_all_done;
     }
+    ITB_TL_ANY(6);
 }
 
 static int kt_for(int beam) { return beam <= 4 ? 4 : (beam <= 8 ? 8 : 16); }

@@ -47,6 +47,8 @@ __device__ __forceinline__ int itb_rows_active(const ItbCtl* ctl) {
 }
 
 #ifndef ITB_TIMELINE
+#define ITB_TL(n) do { } while (0)
+#define ITB_TL_ANY(n) do { } while (0)
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 #else
@@ -66,6 +68,11 @@ __device__ __forceinline__ void itb_tl_stamp(int tag) {
 }
 __device__ __forceinline__ void pdl_wait_impl() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger_impl() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// extra stamps inside a kernel (diagnostic build only): ITB_TL(n) by block 0, ITB_TL_ANY(n) by thread 0 of whichever block runs it
+#define ITB_TL(n) itb_tl_stamp(ITB_TL_FILE * 100000 + 90000 + (n))
+#define ITB_TL_ANY(n) do { if (threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); \
+        const unsigned long long i_ = atomicAdd(&g_itb_tl[0], 1ull); \
+        if (i_ < ITB_TL_CAP) { g_itb_tl[1 + 2 * i_] = (unsigned long long)(ITB_TL_FILE * 100000 + 90000 + (n)); g_itb_tl[2 + 2 * i_] = t_; } } } while (0)
 #define pdl_wait() do { pdl_wait_impl(); itb_tl_stamp(ITB_TL_FILE * 100000 + 50000 + __LINE__); } while (0)
 #define pdl_trigger() do { itb_tl_stamp(ITB_TL_FILE * 100000 + __LINE__); pdl_trigger_impl(); } while (0)
 #endif

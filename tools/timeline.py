@@ -46,9 +46,11 @@ assert n > 0, "no stamps: is ITB_LIB the timeline build?"
 tags, times = buf[1:1 + 2 * n:2].astype(np.int64), buf[2:2 + 2 * n:2].astype(np.int64)
 order = np.argsort(times, kind="stable")
 tags, times = tags[order], times[order]
-dep = (tags % 100000) >= 50000
+sub = (tags % 100000) >= 90000                       # ITB_TL(n) stamps inside a kernel
+dep = ((tags % 100000) >= 50000) & ~sub
 dt, dtime = tags[dep] - 50000, times[dep]
-et, etime = tags[~dep], times[~dep]
+et, etime = tags[~dep & ~sub], times[~dep & ~sub]
+st_, stime = tags[sub], times[sub]
 
 
 def name(tag):
@@ -66,7 +68,7 @@ for t in embed:
             first = (t, gaps.min(), idx)
 t0, period, starts = first
 print("stamps %d (dependency %d, entry %d); step = %d launches, starting at %s; %d whole steps recorded" % (
-    n, dep.sum(), (~dep).sum(), period, name(t0), len(starts) - 1))
+    n, dep.sum(), (~dep & ~sub).sum(), period, name(t0), len(starts) - 1))
 starts = [s for s in starts[1:-1] if s + period < len(dt)]      # skip the first step (cold) and the last (clipped)
 chain = np.array([[dtime[s + k + 1] - dtime[s + k] for k in range(period)] for s in starts], dtype=np.float64) / 1000.0
 # entry stamp of the same kernel instance: the latest entry stamp with that tag at or before the dependency stamp
@@ -74,7 +76,7 @@ res = np.zeros((len(starts), period))
 for i, s in enumerate(starts):
     for k in range(period):
         j = np.searchsorted(etime, dtime[s + k], side="right") - 1
-        while j >= 0 and et[j] != dt[s + k]:
+        while j >= 0 and et[j] // 100000 != dt[s + k] // 100000:      # same source file (entry and dependency stamps differ in line)
             j -= 1
         res[i, k] = (dtime[s + k] - etime[j]) / 1000.0 if j >= 0 else float("nan")
 print("%-4s %-24s %10s %10s %12s" % ("pos", "kernel (dependency stamp)", "chain us", "min us", "resident us"))
@@ -86,3 +88,14 @@ for k in range(period):
     by.setdefault(name(dt[starts[0] + k]), []).append(chain[:, k].mean())
 for kname, v in sorted(by.items(), key=lambda kv: -sum(kv[1])):
     print("  %-24s x%-3d %8.1f us per step  (%.2f us per launch)" % (kname, len(v), sum(v), sum(v) / len(v)))
+if len(st_):
+    print("stamps inside kernels: mean time since the kernel's dependency stamp")
+    for t in np.unique(st_):
+        d = []
+        for tm in stime[st_ == t]:
+            j = np.searchsorted(dtime, tm, side="right") - 1
+            while j >= 0 and dt[j] // 100000 != t // 100000:
+                j -= 1
+            if j >= 0:
+                d.append((tm - dtime[j]) / 1000.0)
+        print("  %s #%d  n=%d  %8.2f us" % (FILES.get(int(t) // 100000, "?"), int(t) % 100000 - 90000, len(d), float(np.mean(d[2:])) if len(d) > 2 else float("nan")))
