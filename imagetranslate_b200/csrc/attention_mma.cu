@@ -47,18 +47,21 @@ struct AttnMmaArgs {
     int M, beam, d, T_max, S, L, layer, n_warps;
 };
 
-// SPLIT (small launches, where a step is bound by the length of one warp's walk and most SMs idle): the AM_WARPS warps of
-// a CTA share ONE item; warp w walks stages w, w + AM_WARPS, ... of the virtual position list and the partial softmax
-// states (max, sum, unnormalised output) are merged through shared memory by warp 0 (split-K for attention).
-template <typename T, bool SELF, int STAGE, bool SPLIT = false>
+// NSPLIT = 2 or 4 (small launches, where a step is bound by the length of one warp's walk and most SMs idle): NSPLIT
+// consecutive warps of a CTA share ONE item; warp w of the team walks stages w, w + NSPLIT, ... of the virtual position
+// list and the partial softmax states (max, sum, unnormalised output) are merged through shared memory by the team's
+// first warp (split-K for attention).  The team synchronises on its own named barrier: teams of one CTA work on
+// different sentences and leave independently.
+template <typename T, bool SELF, int STAGE, int NSPLIT = 1>
 __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(AttnMmaArgs a) {
     pdl_trigger();
+    constexpr bool SPLIT = NSPLIT > 1;
     const int lane = threadIdx.x & 31, nl = lane >> 2, c = lane & 3;       // nl: B-fragment column / C row; c: quad lane
-    const int wsub = SPLIT ? (int)(threadIdx.x >> 5) : 0;                  // SPLIT: this warp's share of the stages
-    constexpr int NSPLIT = SPLIT ? AM_WARPS : 1;
+    const int wsub = (int)(threadIdx.x >> 5) % NSPLIT;                     // this warp's share of the stages
+    const int team = (int)(threadIdx.x >> 5) / NSPLIT;                     // teams per CTA: AM_WARPS / NSPLIT
     const int sb0 = wsub * STAGE;                                          // first virtual position of this warp's first stage
-    const int wg = SPLIT ? (int)blockIdx.x : (int)(blockIdx.x * AM_WARPS + (threadIdx.x >> 5));
-    if (wg >= a.n_warps) return;                                           // SPLIT: uniform over the CTA
+    const int wg = (int)blockIdx.x * (AM_WARPS / NSPLIT) + team;
+    if (wg >= a.n_warps) return;                                           // uniform over the team
     const int d = a.d, H = d / DH, nz = (a.beam + 3) >> 2;
     const int h = wg % H, z = (wg / H) % nz, b = wg / (H * nz);
     const int q0 = z * 4, row0 = b * a.beam + q0, nq = min(4, a.beam - q0);
@@ -199,8 +202,8 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
         }
         tl = pc - cshared + 1;
         nv = cshared + nq * tl;
-        if (SPLIT) __syncthreads();      // the appended rows are read back below by other lanes of this warp (SPLIT: CTA)
-        else __syncwarp();
+        if (SPLIT) asm volatile("bar.sync %0, %1;" ::"r"(1 + team), "r"(32 * NSPLIT) : "memory");   // the appended rows are read back
+        else __syncwarp();                                                                           // below by other lanes (of the team)
     } else {
         base = reinterpret_cast<const T*>(a.kv) + ((size_t)b * a.S * a.L + a.layer) * 2 * d + hoff;
         pos_stride = (size_t)a.L * 2 * d;
@@ -385,12 +388,13 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
         mine[0] = m_run; mine[1] = l_run;
 #pragma unroll
         for (int i = 0; i < 16; ++i) mine[2 + i] = f[i];
-        __syncthreads();
+        asm volatile("bar.sync %0, %1;" ::"r"(1 + team), "r"(32 * NSPLIT) : "memory");
         if (wsub != 0) return;
+        const unsigned char* team_ws = am_smem + (size_t)(team * NSPLIT) * (STAGE * AM_ROWB);
         float mm = m_run;
 #pragma unroll
         for (int w2 = 1; w2 < NSPLIT; ++w2)
-            mm = fmaxf(mm, reinterpret_cast<const float*>(am_smem + (size_t)w2 * (STAGE * AM_ROWB))[lane * 18]);
+            mm = fmaxf(mm, reinterpret_cast<const float*>(team_ws + (size_t)w2 * (STAGE * AM_ROWB))[lane * 18]);
         const float mu = (mm == -INFINITY) ? 0.f : mm;
         const float c0s = __expf(m_run - mu);                             // -inf -> 0: a warp that saw nothing visible
         l_run *= c0s;
@@ -398,7 +402,7 @@ __global__ void __launch_bounds__(AM_THREADS, AM_MINB(STAGE)) attn_mma_kernel(At
         for (int i = 0; i < 16; ++i) f[i] *= c0s;
 #pragma unroll
         for (int w2 = 1; w2 < NSPLIT; ++w2) {
-            const float* oth = reinterpret_cast<const float*>(am_smem + (size_t)w2 * (STAGE * AM_ROWB)) + lane * 18;
+            const float* oth = reinterpret_cast<const float*>(team_ws + (size_t)w2 * (STAGE * AM_ROWB)) + lane * 18;
             const float cs = __expf(oth[0] - mu);
             l_run += oth[1] * cs;
 #pragma unroll
@@ -434,18 +438,19 @@ static int launch_attn_mma_stage(const AttnMmaArgs& a, bool self, cudaStream_t s
     return itb_check_launch(self ? "self_attention" : "cross_attention");
 }
 
-// SPLIT launch: one CTA per item, its four warps sharing the item's stages
-template <typename T>
+// Split launch: NSPLIT warps per item, AM_WARPS / NSPLIT items per CTA
+template <typename T, int NSPLIT>
 static int launch_attn_mma_split(const AttnMmaArgs& a, bool self, cudaStream_t s) {
-    const dim3 grid(a.n_warps), block(AM_THREADS);
+    constexpr int kItems = AM_WARPS / NSPLIT;
+    const dim3 grid((a.n_warps + kItems - 1) / kItems), block(AM_THREADS);
     static bool attr_self[ITB_MAX_DEVICES] = {}, attr_cross[ITB_MAX_DEVICES] = {};
     {
-        cudaError_t e1 = itb_smem_attr_once(attr_self, attn_mma_kernel<T, true, 64, true>, AM_SMEM(64));
-        cudaError_t e2 = itb_smem_attr_once(attr_cross, attn_mma_kernel<T, false, 64, true>, AM_SMEM(64));
+        cudaError_t e1 = itb_smem_attr_once(attr_self, attn_mma_kernel<T, true, 64, NSPLIT>, AM_SMEM(64));
+        cudaError_t e2 = itb_smem_attr_once(attr_cross, attn_mma_kernel<T, false, 64, NSPLIT>, AM_SMEM(64));
         if (e1 != cudaSuccess || e2 != cudaSuccess) { itb_set_error("attention: cudaFuncSetAttribute failed"); return -1; }
     }
-    cudaError_t e = self ? itb_launch(attn_mma_kernel<T, true, 64, true>, grid, block, (size_t)AM_SMEM(64), s, a)
-                         : itb_launch(attn_mma_kernel<T, false, 64, true>, grid, block, (size_t)AM_SMEM(64), s, a);
+    cudaError_t e = self ? itb_launch(attn_mma_kernel<T, true, 64, NSPLIT>, grid, block, (size_t)AM_SMEM(64), s, a)
+                         : itb_launch(attn_mma_kernel<T, false, 64, NSPLIT>, grid, block, (size_t)AM_SMEM(64), s, a);
     if (e != cudaSuccess) { itb_set_error("%s: launch failed: %s", self ? "self_attention" : "cross_attention", cudaGetErrorString(e)); return -1; }
     return itb_check_launch(self ? "self_attention" : "cross_attention");
 }
@@ -454,22 +459,23 @@ template <typename T>
 static int launch_attn_mma(AttnMmaArgs a, bool self, cudaStream_t s) {
     const int B = a.M / a.beam, H = a.d / DH;
     a.n_warps = B * H * ((a.beam + 3) / 4);
-    // Small launches (at most two waves of one-item CTAs, 3 CTAs per SM): the step waits for the longest walk of a single
-    // warp while most of the GPU idles, so the item's stages are shared by the four warps of a CTA.
-    // ITB_ATTN_SPLIT = item count up to which this applies (0: never).
+    // Small launches: the step waits for the longest walk of a single warp while most of the GPU idles, so an item's stages
+    // are shared by four warps (up to one wave of one-item CTAs, 3 CTAs per SM) or two (up to one wave of two-item CTAs).
+    // ITB_ATTN_SPLIT = item count up to which the 4-way split applies, the 2-way split up to twice that (0: never).
     static int split_max = -1;
     if (split_max < 0) {
         const char* e = getenv("ITB_ATTN_SPLIT");
-        split_max = (e != nullptr) ? atoi(e) : 2 * 3 * itb_num_sms();
+        split_max = (e != nullptr) ? atoi(e) : 3 * itb_num_sms();
     }
-    if (a.n_warps <= split_max) return launch_attn_mma_split<T>(a, self, s);
-    // more than ~2 waves of the 3-CTA build (148 SMs x 12 warps): occupancy beats round trips (measured at 4096 rows:
-    // step -28 us; at 244 rows the 64-position build is 25 us per step faster)
-    static int forced = -1;
+    static int forced = -1;              // ITB_ATTN_STAGE = 32 / 64: that unsplit build for every launch (tests, A/B timing)
     if (forced < 0) {
         const char* e = getenv("ITB_ATTN_STAGE");
         forced = (e != nullptr) ? atoi(e) : 0;
     }
+    if (forced == 0 && a.n_warps <= split_max) return launch_attn_mma_split<T, 4>(a, self, s);
+    if (forced == 0 && a.n_warps <= 2 * split_max) return launch_attn_mma_split<T, 2>(a, self, s);
+    // more than ~2 waves of the 3-CTA build (148 SMs x 12 warps): occupancy beats round trips (measured at 4096 rows:
+    // step -28 us; at 244 rows the 64-position build is 25 us per step faster)
     const bool small_stage = forced != 0 ? forced == 32 : a.n_warps > 2 * itb_num_sms() * 12;
     return small_stage ? launch_attn_mma_stage<T, 32>(a, self, s) : launch_attn_mma_stage<T, 64>(a, self, s);
 }

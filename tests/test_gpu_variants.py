@@ -4,7 +4,10 @@ in a child process (the switches are read once per process) so the small parity 
    only selects for launches of more than ~2 waves (4096 beam rows); ITB_ATTN_STAGE=64 is the small-launch build;
  * ITB_VOCAB_PAIR=1 -- the CTA-pair (tcgen05 cta_group::2) launch of the fused vocabulary projection;
  * ITB_ATTN_BULK=1 / 0 -- the bulk-copy producer / consumer attention kernel (csrc/attention_bulk.cu), which the library
-   selects for launches of >= 96 work items (sentences x beam groups), forced on for every 16-bit attention launch / off."""
+   selects for launches of >= 96 work items (sentences x beam groups), forced on for every 16-bit attention launch / off;
+ * ITB_ATTN_SPLIT=N -- the warp-per-head attention kernel shares an item's stages among 4 warps up to N items and among 2 up to
+   2N (default N = 3 x SM count, so the small parity cases run the 4-way split): 20 puts the kernel tests (36 items and
+   more) on the 2-way split, 0 on the unsplit kernel that large launches use."""
 import os
 import subprocess
 import sys
@@ -27,6 +30,15 @@ def _run(env, select, path="tests/test_gpu_kernels.py"):
 @pytest.mark.parametrize("stage", ["32", "64"])
 def test_attention_kernels_in_both_staging_builds(stage):
     _run({"ITB_ATTN_STAGE": stage}, "attention")
+
+
+@pytest.mark.parametrize("split", ["0", "20"])
+def test_attention_kernels_unsplit_and_two_way_split(split):
+    _run({"ITB_ATTN_SPLIT": split}, "attention")
+
+
+def test_decode_parity_on_the_two_way_split_attention():
+    _run({"ITB_ATTN_SPLIT": "40"}, "16bit or forward_many", path="tests/test_gpu_decode.py")       # 37..80 items: two warps per item
 
 
 def test_decode_parity_with_the_many_wave_attention_build():
