@@ -14,6 +14,9 @@ int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const v
                 int M, int N, int K, int ldo, int act_f16, int mt, int nsplit, cudaStream_t s);
 int itb_make_tmap_16b(CUtensorMap* map, const void* base, int rows, int K, int box_rows, int is_f16);
 void itb_tc_plan(int M, int N, int K, int max_split, int* mt_out, int* split_out);
+bool itb_tc_pair_applies(int M, int N, int K);
+int itb_gemm_tc_pair(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA128, const void* ctl, const float* bias, void* out,
+                     int M, int N, int K, int ldo, int act_f16, cudaStream_t s);
 int itb_gemm_tc_vocab(int kt, const CUtensorMap* tmX, const CUtensorMap* tmWv, const CUtensorMap* tmWv128, const void* ctl,
                       const float* bias, int rows, int V, int K, int act_f16, float* cand_val, int* cand_idx, float* chunk_max,
                       float* chunk_sum, float* logits, int ldl, int n_chunk, cudaStream_t s);
@@ -56,17 +59,20 @@ struct Linear {
     int M = 0, N = 0, K = 0, ldo = 0, epi = 0;
     int max_split = 1;       // > 1: `out` is [max_split][M][ldo] and the consumer sums `nsplit` partial outputs
     int mt = 32, nsplit = 1;
-    bool tc = false;
+    bool tc = false, pair = false;   // pair: CTA-pair launch (256 x 256 tiles, no split-K; gemm_tc.cu)
     CUtensorMap tmW, tmA;
     int prepare(int dtype, int impl) {
         tc = use_tc(dtype, impl);
         if (!tc) return 0;
-        itb_tc_plan(M, N, K, max_split, &mt, &nsplit);
+        pair = itb_tc_pair_applies(M, N, K);
+        if (pair) { mt = 128; nsplit = 1; }
+        else itb_tc_plan(M, N, K, max_split, &mt, &nsplit);
         int r = itb_make_tmap_16b(&tmW, W, N, K, 128, dtype == ITB_F16 ? 1 : 0);
         if (r != 0) return r;
         return itb_make_tmap_16b(&tmA, A, M, K, mt, dtype == ITB_F16 ? 1 : 0);
     }
     int run(int dtype, const void* ctl, cudaStream_t s) const {
+        if (tc && pair) return itb_gemm_tc_pair(epi, &tmW, &tmA, ctl, bias, out, M, N, K, ldo, dtype == ITB_F16 ? 1 : 0, s);
         if (tc) return itb_gemm_tc(epi, &tmW, &tmA, ctl, bias, out, M, N, K, ldo, dtype == ITB_F16 ? 1 : 0, mt, nsplit, s);
         return itb_gemm_simt(dtype, epi, ctl, A, W, bias, out, M, N, K, ldo, s);
     }

@@ -532,16 +532,20 @@ __device__ __forceinline__ void tc_epilogue_vocab(uint32_t tmem_base, uint64_t* 
 // Epilogue of warps 4-11: TMEM lane = weight row n (this lane), TMEM column = activation row m.  Per 32-column chunk one
 // tcgen05.ld, then 32 stores out[m][n] that are coalesced across the warp (consecutive n); the row pointer advances by
 // ldo per column, full chunks take a path without per-element bounds checks.
-template <int MT, int EPI, typename OT>
+// PAIR (gemm_tc2_kernel): tiles are walked per CTA pair (256 weight rows x 256 activation rows); this CTA owns the weight
+// rows of 128-row tile 2 * (pair's tile) + rank, and hands the accumulator back on the LEADER's barrier (tempty_remote).
+template <int MT, int EPI, typename OT, bool PAIR = false>
 __device__ __forceinline__ void tc_epilogue(uint32_t tmem_base, uint64_t* tfull, uint64_t* tempty, const float* __restrict__ bias,
                                             OT* __restrict__ out, int M, int N, int ldo, int nsplit, size_t part_stride,
-                                            int total, int m_tiles, int warp, int lane, int rows_act) {
+                                            int total, int m_tiles, int warp, int lane, int rows_act, uint32_t tempty_remote = 0u) {
     const int q = warp & 3;                                 // TMEM lane quarter this warp may access
     const int half = (warp - 4) >> 2;                       // which half of the tile's columns this warp drains
     constexpr int CH = (MT / 2 < 32) ? 32 : MT / 2;         // MT = 32: the second warp of the quarter has no columns
     uint32_t as = 0, aphase = 0;
-    for (int t = blockIdx.x; t < total; t += gridDim.x) {
-        const int ks = t % nsplit, mt = (t / nsplit) % m_tiles, nt = (t / nsplit) / m_tiles;
+    const int t0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, tstep = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    for (int t = t0; t < total; t += tstep) {
+        const int ks = PAIR ? 0 : t % nsplit, mt = PAIR ? t % m_tiles : (t / nsplit) % m_tiles;
+        const int nt = PAIR ? 2 * (t / m_tiles) + (int)(blockIdx.x & 1) : (t / nsplit) / m_tiles;
         if (mt * MT >= rows_act) continue;                  // rows of finished groups only (see tc_tile_dead)
         mbar_wait(&tfull[as], aphase);
         tc_fence_after();
@@ -577,7 +581,8 @@ __device__ __forceinline__ void tc_epilogue(uint32_t tmem_base, uint64_t* tfull,
             }
         }
         tc_fence_before();
-        mbar_arrive(&tempty[as]);
+        if (PAIR) mbar_arrive_cluster(tempty_remote + 8u * as);
+        else mbar_arrive(&tempty[as]);
         if (++as == 2) { as = 0; aphase ^= 1; }
     }
 }
@@ -858,6 +863,156 @@ gemm_tc2_vocab_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_cons
     }
 }
 
+// ---------------------------------- layer GEMMs on CTA pairs (large M; opt-in, see itb_tc_pair_applies) ----------------------------------
+// out[M][N] = epi(A . W^T + b) like gemm_tc_kernel, but ONE tile of 256 weight rows x 256 activation rows per CTA PAIR
+// (tcgen05.mma.cta_group::2, M = 256, N = 256).  A single-CTA 128 x 256 tile pulls (128 + 256) x 128 B per k-block through L2
+// for 128 x 256 x 64 MACs (85 flop/B), the pair tile (128 + 128) x 128 B per CTA for the same MACs (128 flop/B).  Each CTA stages its own 128 weight rows (UMMA A: TMEM lane =
+// weight row, as in gemm_tc_kernel, so the epilogue is the same) and 128 of the tile's 256 activation rows (its half of
+// UMMA B).  Barrier protocol as in gemm_tc2_vocab_kernel: the leader (rank 0) owns "stage full" and "accumulator drained"
+// and issues the MMAs; "stage free" and "accumulator ready" are multicast to both CTAs by tcgen05.commit.  No split-K.
+#define TC2L_STAGES 6
+#define TC2L_SMEM (TC2L_STAGES * 2 * TC2_HALF_BYTES + 1024 + 256)
+
+__device__ __forceinline__ uint32_t ld_shared_cluster_u32(uint32_t cluster_addr) {
+    uint32_t v;
+    asm volatile("ld.shared::cluster.u32 %0, [%1];" : "=r"(v) : "r"(cluster_addr) : "memory");
+    return v;
+}
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
+                const ItbCtl* __restrict__ ctl, const float* __restrict__ bias, void* __restrict__ out, int M, int N, int K,
+                int ldo, int act_f16) {
+    extern __shared__ uint8_t smem_raw[];
+    pdl_trigger();
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem_w = smem;                                           // [stages][128 weight rows][64]      (UMMA A, this CTA's rows)
+    uint8_t* smem_a = smem + TC2L_STAGES * TC2_HALF_BYTES;            // [stages][128 activation rows][64]  (this CTA's half of UMMA B)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TC2L_STAGES * 2 * TC2_HALF_BYTES);
+    uint64_t* full = bars;                     // leader's is used: expects both CTAs' bytes
+    uint64_t* empty = bars + TC2L_STAGES;      // per CTA, multicast arrival
+    uint64_t* tfull = bars + 2 * TC2L_STAGES;  // per CTA, multicast arrival
+    uint64_t* tempty = tfull + 2;              // leader's is used: 256 epilogue threads of each CTA
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);    // [0] TMEM base, [1] rows_active (the leader's reading, for both)
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    const int pair = blockIdx.x >> 1, npair = gridDim.x >> 1;
+    const int m_tiles = (M + 255) / 256, n_tiles = (N + 255) / 256, total = m_tiles * n_tiles, KB = K / TC_BK;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmW)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < TC2L_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 512); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // Both CTAs must agree on which tiles are dead: the leader reads rows_active (before the dependency wait: a stale value
+    // is a LARGER one, see gemm_tc_kernel) into its shared memory ahead of the cluster barrier; the peer reads it from there.
+    if (threadIdx.x == 96 && rank == 0) tmem_slot[1] = (uint32_t)itb_rows_active(ctl);
+    __syncthreads();
+    cluster_sync_all();                        // both CTAs' barriers exist before any remote arrival / TMEM pairing
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int rows_act = (int)ld_shared_cluster_u32(cluster_addr_of(smem_u32(&tmem_slot[1]), 0));
+    const uint32_t full_l = cluster_addr_of(smem_u32(full), 0), tempty_l = cluster_addr_of(smem_u32(tempty), 0);
+    int tfirst = pair;                         // the pair's first live tile (tile t: activation tile t % m_tiles, weight tile t / m_tiles)
+    while (tfirst < total && (tfirst % m_tiles) * 256 >= rows_act) tfirst += npair;
+
+    // the weight rows of the first stages are requested before the programmatic-dependency wait (weights are static)
+    int pre = 0;
+    if (warp == 0 && lane == 0 && tfirst < total) {
+        const int nt = tfirst / m_tiles;
+        pre = KB < TC2L_STAGES ? KB : TC2L_STAGES;
+        for (int kb = 0; kb < pre; ++kb) {
+            if (rank == 0) mbar_expect_tx(&full[kb], 4 * TC2_HALF_BYTES);
+            tma_load_2d_pair(smem_w + kb * TC2_HALF_BYTES, &tmW, kb * TC_BK, nt * 256 + (int)rank * 128, full_l + 8u * kb);
+        }
+    }
+    pdl_wait();
+    const bool done = (ctl != nullptr) && (ctl->done != 0);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            if (tfirst < total) {
+                const int mt = tfirst % m_tiles;
+                for (int kb = 0; kb < pre; ++kb)
+                    tma_load_2d_pair(smem_a + kb * TC2_HALF_BYTES, &tmA, kb * TC_BK, mt * 256 + (int)rank * 128, full_l + 8u * kb);
+                if (done && rank == 0)                 // search already terminated: drain both CTAs' copies, then leave
+                    for (int kb = 0; kb < pre; ++kb) mbar_wait(&full[kb], 0);
+            }
+            if (!done) {
+                uint32_t stage = (pre == TC2L_STAGES) ? 0 : pre, phase = (pre == TC2L_STAGES) ? 1 : 0;
+                int kb0 = pre;
+                for (int t = tfirst; t < total; t += npair) {
+                    const int mt = t % m_tiles, nt = t / m_tiles;
+                    if (mt * 256 >= rows_act) continue;
+                    for (int kb = kb0; kb < KB; ++kb) {
+                        mbar_wait(&empty[stage], phase ^ 1);
+                        if (rank == 0) mbar_expect_tx(&full[stage], 4 * TC2_HALF_BYTES);
+                        tma_load_2d_pair(smem_w + stage * TC2_HALF_BYTES, &tmW, kb * TC_BK, nt * 256 + (int)rank * 128, full_l + 8u * stage);
+                        tma_load_2d_pair(smem_a + stage * TC2_HALF_BYTES, &tmA, kb * TC_BK, mt * 256 + (int)rank * 128, full_l + 8u * stage);
+                        if (++stage == TC2L_STAGES) { stage = 0; phase ^= 1; }
+                    }
+                    kb0 = 0;
+                }
+            }
+        }
+    } else if (done) {
+        // nothing to compute
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            // D = f32; A, B formats equal (bf16 = 1 / f16 = 0); both K-major; N = 256 (>>3 @17); M = 256 over the pair (>>4 @24)
+            const uint32_t idesc = (1u << 4) | ((act_f16 ? 0u : 1u) << 7) | ((act_f16 ? 0u : 1u) << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+            uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+            for (int t = tfirst; t < total; t += npair) {
+                if ((t % m_tiles) * 256 >= rows_act) continue;
+                mbar_wait(&tempty[as], aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * 256;
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint64_t dw = make_sw128_desc(smem_u32(smem_w + stage * TC2_HALF_BYTES));
+                    const uint64_t da = make_sw128_desc(smem_u32(smem_a + stage * TC2_HALF_BYTES));
+#pragma unroll
+                    for (int k = 0; k < TC_BK / 16; ++k)
+                        umma_bf16_pair(d_tmem, dw + 2 * k, da + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                    umma_commit_pair(&empty[stage]);
+                    if (++stage == TC2L_STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_pair(&tfull[as]);
+                if (++as == 2) { as = 0; aphase ^= 1; }
+            }
+        }
+    } else if (warp >= 4) {
+        if constexpr (EPI == ITB_EPI_BIAS_F32)
+            tc_epilogue<256, EPI, float, true>(tmem_base, tfull, tempty, bias, reinterpret_cast<float*>(out), M, N, ldo, 1, (size_t)0, total, m_tiles, warp, lane, rows_act, tempty_l);
+        else if (act_f16)
+            tc_epilogue<256, EPI, __half, true>(tmem_base, tfull, tempty, bias, reinterpret_cast<__half*>(out), M, N, ldo, 1, (size_t)0, total, m_tiles, warp, lane, rows_act, tempty_l);
+        else
+            tc_epilogue<256, EPI, __nv_bfloat16, true>(tmem_base, tfull, tempty, bias, reinterpret_cast<__nv_bfloat16*>(out), M, N, ldo, 1, (size_t)0, total, m_tiles, warp, lane, rows_act, tempty_l);
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                        // the peer's shared memory / barriers stay alive until both CTAs are through
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
 // ------------------------------------------------ host side ------------------------------------------------
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -962,6 +1117,49 @@ int itb_gemm_tc(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA, const v
         case 256: return launch_tc_epi<256>(epi, *tmW, *tmA, c, bias, out, M, N, K, ldo, act_f16, nsplit, s);
         default: itb_set_error("linear(tcgen05): unsupported tile height %d", mt); return -2;
     }
+}
+
+// CTA-pair launch of a layer GEMM (gemm_tc2_kernel): tmW and tmA128 both with 128-row boxes.
+template <int EPI>
+static int launch_tc2(const CUtensorMap& tmW, const CUtensorMap& tmA128, const ItbCtl* ctl, const float* bias, void* out, int M, int N,
+                      int K, int ldo, int act_f16, cudaStream_t s) {
+    static bool attr_set[ITB_MAX_DEVICES] = {};
+    {
+        cudaError_t e = itb_smem_attr_once(attr_set, gemm_tc2_kernel<EPI>, TC2L_SMEM);
+        if (e != cudaSuccess) { itb_set_error("gemm_tc2: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return -1; }
+    }
+    const int total = ((N + 255) / 256) * ((M + 255) / 256);
+    const int cap = num_sms() & ~1;
+    const int grid = 2 * total < cap ? 2 * total : cap;
+    cudaError_t e = itb_launch(gemm_tc2_kernel<EPI>, dim3(grid), dim3(TC_THREADS), (size_t)TC2L_SMEM, s, tmW, tmA128, ctl, bias, out, M, N, K,
+                               ldo, act_f16);
+    if (e != cudaSuccess) { itb_set_error("gemm_tc2: launch failed: %s", cudaGetErrorString(e)); return -1; }
+    return itb_check_launch("gemm_tc2");
+}
+
+int itb_gemm_tc_pair(int epi, const CUtensorMap* tmW, const CUtensorMap* tmA128, const void* ctl, const float* bias, void* out,
+                     int M, int N, int K, int ldo, int act_f16, cudaStream_t s) {
+    ITB_REQUIRE(K % TC_BK == 0 && K >= TC_BK, "linear(tcgen05 pair): K must be a multiple of 64");
+    const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
+    if (epi == ITB_EPI_BIAS_F32) return launch_tc2<ITB_EPI_BIAS_F32>(*tmW, *tmA128, c, bias, out, M, N, K, ldo, act_f16, s);
+    if (epi == ITB_EPI_BIAS_GELU_ACT) return launch_tc2<ITB_EPI_BIAS_GELU_ACT>(*tmW, *tmA128, c, bias, out, M, N, K, ldo, act_f16, s);
+    return launch_tc2<ITB_EPI_BIAS_ACT>(*tmW, *tmA128, c, bias, out, M, N, K, ldo, act_f16, s);
+}
+
+// Whether a layer GEMM of this shape runs on CTA pairs.  Opt-in: ITB_GEMM_PAIR=1 every shape (tests), =2 wide outputs at
+// large M (N >= 1536, M >= 1024: QKV and FFN1 of a super-batch; N = 768 makes only 3 x ceil(M / 256) pair tiles, too few for
+// 74 pairs).  Measured at 4096 rows (profiles/r2_gemm_pair_ab.txt): QKV 15.6 -> 15.9 us, FFN1 + GELU 25.2 -> 25.6 us -- the
+// single-CTA launches are not bound by the operand feed the pairing halves (tensor pipe active 39-44 % with the issue
+// slots 17 % busy: what is left is fill / drain of 2-3 tiles per CTA), so the default stays on the single-CTA plan.
+bool itb_tc_pair_applies(int M, int N, int K) {
+    static int mode = -1;
+    if (mode < 0) {
+        const char* e = getenv("ITB_GEMM_PAIR");
+        mode = (e == nullptr) ? 0 : atoi(e);
+    }
+    if (mode == 0 || K % TC_BK != 0) return false;
+    if (mode == 1) return true;
+    return N >= 1536 && M >= 1024;
 }
 
 // Fused vocabulary projection (operands swapped: tmX = activations [rows][K] box 128, tmWv = weights [V][K] box 256,

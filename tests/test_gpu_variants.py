@@ -3,6 +3,7 @@ in a child process (the switches are read once per process) so the small parity 
  * ITB_ATTN_STAGE=32 -- the 32-position / 4-CTAs-per-SM build of the tensor-core attention kernel, which the library
    only selects for launches of more than ~2 waves (4096 beam rows); ITB_ATTN_STAGE=64 is the small-launch build;
  * ITB_VOCAB_PAIR=1 -- the CTA-pair (tcgen05 cta_group::2) launch of the fused vocabulary projection;
+ * ITB_GEMM_PAIR=1 -- the CTA-pair launch of the layer GEMMs (gemm_tc2_kernel), opt-in like the one above;
  * ITB_ATTN_BULK=1 / 0 -- the bulk-copy producer / consumer attention kernel (csrc/attention_bulk.cu), which the library
    selects for launches of >= 96 work items (sentences x beam groups), forced on for every 16-bit attention launch / off;
  * ITB_ATTN_SPLIT=N -- the warp-per-head attention kernel shares an item's stages among 4 warps up to N items and among 2 up to
@@ -43,6 +44,13 @@ def test_decode_parity_on_the_two_way_split_attention():
 
 def test_decode_parity_with_the_many_wave_attention_build():
     _run({"ITB_ATTN_STAGE": "32"}, "16bit or forward_many or encoder", path="tests/test_gpu_decode.py")
+
+
+def test_layer_gemms_on_cta_pairs():
+    """ITB_GEMM_PAIR=1: every tcgen05 linear (all shapes of test_linear_*, ragged M and N included) through the
+    cta_group::2 kernel with 256 x 256 tiles; then a whole decode on it"""
+    _run({"ITB_GEMM_PAIR": "1"}, "linear")
+    _run({"ITB_GEMM_PAIR": "1"}, "teacher_forced_logprob_error or free_running or forward_many", path="tests/test_gpu_decode.py")
 
 
 def test_fused_vocab_projection_on_cta_pairs():
