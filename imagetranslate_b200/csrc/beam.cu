@@ -300,32 +300,40 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
                 logz = logf(ss);
                 ITB_TL(11);
                 // T = K-th largest chunk maximum (a real logit each): a lower bound of the row's K-th largest logit, so
-                // only chunks whose maximum reaches T can hold a top-K entry -- typically K..2K of them
-                float tl = -INFINITY, T = -INFINITY;
+                // only chunks whose maximum reaches T can hold a top-K entry -- typically K..2K of them.  K rounds of
+                // "largest remaining maximum" (local maximum of the lane's 16, warp maximum, the lowest lane that holds it
+                // gives up one slot) name the first K chunks of the queue directly; the chunks that TIE with T follow.
+                float cw[CPL];                                       // working copy: extracted slots become -inf
 #pragma unroll
-                for (int j = 0; j < CPL; ++j) {
-                    unsigned q = __ballot_sync(0xffffffffu, cmr[j] > T);
-                    while (q != 0u) {
-                        const int src = __ffs(q) - 1;
-                        q &= q - 1;
-                        const float cx = __shfl_sync(0xffffffffu, cmr[j], src);
-                        if (cx > T) {                                        // warp-uniform; T may have risen meanwhile
-                            const int pos = __popc(__ballot_sync(0xffffffffu, lane < K && tl >= cx));
-                            const float uv = __shfl_up_sync(0xffffffffu, tl, 1);
-                            if (lane < K) {
-                                if (lane == pos) tl = cx;
-                                else if (lane > pos) tl = uv;
-                            }
-                            T = __shfl_sync(0xffffffffu, tl, K - 1);
+                for (int j = 0; j < CPL; ++j) cw[j] = cmr[j];
+                float T = -INFINITY;
+                int cnt = 0;
+                for (int k = 0; k < K; ++k) {
+                    float lm = cw[0];
+#pragma unroll
+                    for (int j = 1; j < CPL; ++j) lm = fmaxf(lm, cw[j]);
+                    const float wm = warp_max(lm);
+                    if (wm == -INFINITY) break;                      // fewer than K chunks hold anything (warp-uniform)
+                    T = wm;
+                    const int wl = __ffs(__ballot_sync(0xffffffffu, lm == wm)) - 1;
+                    if (lane == wl) {
+                        int js = 0;
+                        bool found = false;
+#pragma unroll
+                        for (int j = 0; j < CPL; ++j) {
+                            const bool hit = !found && cw[j] == wm;
+                            if (hit) { js = j; cw[j] = -INFINITY; }
+                            found = found || hit;
                         }
+                        s_q[w][cnt] = js * 32 + lane;
                     }
+                    ++cnt;
                 }
                 ITB_TL(12);
-                // queue the qualifying chunks (compacted over the warp), insert them 32 at a time
-                int cnt = 0;
+                // chunks whose maximum ties with T (equal logits in different chunks: the lower index must win, so they count)
 #pragma unroll
                 for (int j = 0; j < CPL; ++j) {
-                    const bool mine = cmr[j] >= T && cmr[j] > -INFINITY;
+                    const bool mine = cw[j] == T && T > -INFINITY;
                     const unsigned bal = __ballot_sync(0xffffffffu, mine);
                     if (bal != 0u) {
                         if (mine) s_q[w][cnt + __popc(bal & ((1u << lane) - 1u))] = j * 32 + lane;
