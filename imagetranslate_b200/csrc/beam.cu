@@ -242,9 +242,9 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
             float thr = -INFINITY;
             // inserts the KT candidates of up to 32 chunks (lane l < k owns chunk s_q[w][l]): one round trip for all of
             // them, then rank by rank with the list's threshold
-            auto insert_chunks = [&](int k) {
+            auto insert_chunks = [&](int base, int k) {
                 const bool mine = lane < k;
-                const int ci = mine ? s_q[w][lane] : 0;
+                const int ci = mine ? s_q[w][base + lane] : 0;
                 float xv[KT]; int xj[KT];
 #pragma unroll
                 for (int u = 0; u < KT; u += 4) {
@@ -278,7 +278,8 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
                 }
             };
             constexpr int CPL = 16;                                  // chunks per lane held in registers
-            if (nc <= 32 * CPL) {
+            bool streamed = nc > 32 * CPL;                           // the generic, streaming form below
+            if (!streamed) {
                 // ---- the usual case (V <= 65536): every chunk maximum / sum of the row is loaded ONCE, all loads in
                 //      flight together; the passes below (max, sum, threshold, queue) run from registers -- the looped
                 //      form paid a dependent memory round trip per 32 chunks and pass, which was the whole kernel ----
@@ -330,30 +331,29 @@ __global__ void __launch_bounds__(256) beam_step_kernel(BeamArgs a) {
                     ++cnt;
                 }
                 ITB_TL(12);
-                // chunks whose maximum ties with T (equal logits in different chunks: the lower index must win, so they count)
+                // chunks whose maximum ties with T (equal logits in different chunks: the lower index must win, so they count).
+                // The queue holds 64 chunks; a row with more (hundreds of equal maxima) takes the streaming form below.
+                // (One copy of the insertion code for the whole kernel path: 17 inlined copies cost more in instruction
+                // fetch than the ranking itself.)
 #pragma unroll
                 for (int j = 0; j < CPL; ++j) {
                     const bool mine = cw[j] == T && T > -INFINITY;
                     const unsigned bal = __ballot_sync(0xffffffffu, mine);
                     if (bal != 0u) {
-                        if (mine) s_q[w][cnt + __popc(bal & ((1u << lane) - 1u))] = j * 32 + lane;
-                        cnt += __popc(bal);
-                        if (cnt >= 32) {
-                            __syncwarp();
-                            insert_chunks(32);
-                            const int rem = cnt - 32;
-                            const int mv = lane < rem ? s_q[w][32 + lane] : 0;
-                            __syncwarp();
-                            if (lane < rem) s_q[w][lane] = mv;
-                            cnt = rem;
+                        if (cnt + __popc(bal) > 64) streamed = true;
+                        else {
+                            if (mine) s_q[w][cnt + __popc(bal & ((1u << lane) - 1u))] = j * 32 + lane;
+                            cnt += __popc(bal);
                         }
                     }
                 }
                 __syncwarp();
                 ITB_TL(13);
-                if (cnt > 0) insert_chunks(cnt);
+                if (!streamed)
+                    for (int base = 0; base < cnt; base += 32) insert_chunks(base, min(32, cnt - base));
                 ITB_TL(14);
-            } else {
+            }
+            if (streamed) {
                 mm = -INFINITY;
                 for (int ci = lane; ci < nc; ci += 32) mm = fmaxf(mm, __ldcg(cmp + ci));
                 mm = warp_max(mm);

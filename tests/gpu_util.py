@@ -71,6 +71,31 @@ class BeamHarness(object):
         _lib.check(_lib.lib().itb_beam_step(C.byref(self.cfg), stream()), "beam_step")
         torch.cuda.synchronize()
 
+    def step_fused(self, logits):
+        """The 16-bit modes' flow: the per-chunk partials that the vocabulary GEMM's epilogue would emit (chunks of 128
+        entries: maximum, sum exp(x - max), top-KT by value desc / index asc) are computed here with torch from `logits`,
+        then itb_beam_step runs with fused_vocab = 1 (phase 2 only, one CTA per sentence)."""
+        l = _lib.lib()
+        nc, KT = l.itb_vocab_chunks(self.V), l.itb_topk_capacity(self.beam)
+        assert nc == self.cfg.n_chunk
+        x = torch.full((self.M, nc * 128), float("-inf"), device=DEV)
+        x[:, :self.V] = logits.to(DEV)
+        x = x.view(self.M, nc, 128)
+        cm = x.max(dim=2).values
+        safe = torch.where(torch.isinf(cm), torch.zeros_like(cm), cm)
+        cs = torch.exp(x - safe[:, :, None]).sum(dim=2)
+        order = torch.argsort(x, dim=2, descending=True, stable=True)[:, :, :KT]
+        cv = torch.gather(x, 2, order)
+        ci = (order + (torch.arange(nc, device=DEV) * 128)[None, :, None]).to(torch.int32)
+        ci = torch.where(torch.isinf(cv), torch.full_like(ci, -1), ci)
+        self.t["chunk_max"].copy_(cm.reshape(-1))
+        self.t["chunk_sum"].copy_(cs.reshape(-1))
+        self.t["cand_val"].copy_(cv.reshape(-1))
+        self.t["cand_idx"].copy_(ci.reshape(-1))
+        self.cfg.fused_vocab = 1
+        _lib.check(l.itb_beam_step(C.byref(self.cfg), stream()), "beam_step")
+        torch.cuda.synchronize()
+
     def state(self):
         ctl = self.ctl()
         cur, n = ctl[3], ctl[2] + 1

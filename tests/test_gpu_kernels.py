@@ -285,6 +285,43 @@ def test_beam_step_matches_reference_semantics(beam, V, n_chunk):
     assert h.ctl()[2] >= 3
 
 
+@pytest.mark.parametrize("beam,V,quantum", [(4, 60000, 0.0), (4, 60000, 0.25), (4, 60000, 8.0), (8, 30000, 0.5), (12, 9000, 0.0),
+                                            (1, 60000, 1.0)])
+def test_beam_step_on_fused_vocabulary_partials(beam, V, quantum):
+    """The 16-bit flow of the search step: phase 2 over per-chunk partials (470 chunks at V = 60000).  quantum > 0 rounds the
+    logits to multiples of it, so that hundreds of chunk maxima are EQUAL: the K-th largest chunk maximum then ties with
+    more chunks than the warp's queue holds and the row is ranked by the streaming form; ties resolve to the lowest index
+    (reference: torch.topk on the flat (beam x V) scores, src/seq_gen.py:203)."""
+    B, T, eos, pad, alpha = 3, 8, 4, 0, 0.8
+    max_lens = [8, 4, 8]
+    first = [6] * B
+    nc = _lib.lib().itb_vocab_chunks(V)
+    h = BeamHarness(B, beam, V, T, max_lens, first, max_len=T, pad=pad, eos=eos, alpha=alpha, n_chunk=nc)
+    prefixes, scores = torch.tensor(first).view(B, 1), torch.zeros(B, 1)
+    sizes = torch.zeros(B) if beam > 1 else None
+    mlt = torch.tensor(max_lens)
+    g = torch.Generator().manual_seed(300 + beam)
+    for i in range(1, T):
+        cur = prefixes.view(-1, prefixes.size(-1))
+        if int(torch.any(cur == eos, 1).sum()) == cur.size(0):
+            break
+        M = B * beam
+        logits = torch.randn(M, V, generator=g) * 2.0
+        if quantum > 0:
+            logits = torch.round(logits / quantum) * quantum
+        if i == 3:
+            logits[torch.randperm(M, generator=g)[: M // 3], eos] += 40.0
+        h.step_fused(logits)
+        rows = logits if i > 1 else logits.view(B, beam, V)[:, 0]
+        logp = torch.log_softmax(rows, -1)
+        prefixes, scores, sizes, _ = R.search_step(i, logp, prefixes, scores, sizes, mlt, eos, pad, beam, alpha,
+                                                   topk_fn=R.lowest_index_topk)
+        tok, sc, sz, anc = h.state()
+        assert tok.tolist() == prefixes.tolist(), "prefixes differ at step %d" % i
+        assert torch.allclose(sc, scores, rtol=1e-5, atol=2e-6), "scores differ at step %d" % i
+    assert h.ctl()[2] >= 3
+
+
 def test_beam_step_is_a_noop_after_termination():
     h = BeamHarness(2, 4, 1000, 6, [6, 6], [6, 6], max_len=3)
     h.step(torch.randn(8, 1000))
