@@ -23,27 +23,29 @@ __device__ __forceinline__ void store4(__half* p, float4 o) {
     *reinterpret_cast<uint2*>(p) = u;
 }
 
-template <typename TA>
+// NVC > 0: d = 128 * NVC is known at compile time -- the column guards fold away and the loads of a row can be issued
+// together instead of one dependent round trip after the other (see add_ln_fast_kernel).
+template <typename TA, int NVC = 0>
 __device__ __forceinline__ void ln_row_write(float4* v, int nv, int d, const float* __restrict__ g, const float* __restrict__ b,
                                              float eps, float* __restrict__ of, TA* __restrict__ oa, int lane) {
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < LN_MAXV; ++i)
-        if (i < nv) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+        if (NVC ? i < NVC : i < nv) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
     const float mean = warp_sum(s) / (float)d;
     float q = 0.f;
 #pragma unroll
     for (int i = 0; i < LN_MAXV; ++i)
-        if (i < nv) {
+        if (NVC ? i < NVC : i < nv) {
             float a0 = v[i].x - mean, a1 = v[i].y - mean, a2 = v[i].z - mean, a3 = v[i].w - mean;
             q += (a0 * a0 + a1 * a1) + (a2 * a2 + a3 * a3);
         }
     const float rstd = rsqrtf(warp_sum(q) / (float)d + eps);
 #pragma unroll
     for (int i = 0; i < LN_MAXV; ++i)
-        if (i < nv) {
+        if (NVC ? i < NVC : i < nv) {
             const int c = (i * 32 + lane) * 4;
-            if (c < d) {
+            if (NVC || c < d) {
                 const float4 gg = *reinterpret_cast<const float4*>(g + c), bb = *reinterpret_cast<const float4*>(b + c);
                 float4 o;
                 o.x = (v[i].x - mean) * rstd * gg.x + bb.x;
@@ -56,13 +58,14 @@ __device__ __forceinline__ void ln_row_write(float4* v, int nv, int d, const flo
         }
 }
 
-template <typename TA>
-__global__ void __launch_bounds__(32 * LN_ROWS, 4) embed_ln_kernel(const ItbCtl* __restrict__ ctl, const int* __restrict__ tokens,
+template <typename TA, int NVC = 0>
+__global__ void __launch_bounds__(32 * LN_ROWS, NVC ? 2 : 4) embed_ln_kernel(const ItbCtl* __restrict__ ctl, const int* __restrict__ tokens,
                                                        const int* __restrict__ tgt_lang, const float* __restrict__ word,
                                                        const float* __restrict__ pos, const float* __restrict__ type,
                                                        const float* __restrict__ g, const float* __restrict__ b, float eps,
                                                        float* __restrict__ x_f32, TA* __restrict__ x_act, int M, int beam,
-                                                       int d, int T_max) {
+                                                       int d_rt, int T_max) {
+    const int d = NVC ? 128 * NVC : d_rt;
     pdl_trigger();
     pdl_wait();
     const int4 c4 = *reinterpret_cast<const int4*>(ctl);          // {step, done, steps_run, cur}
@@ -78,7 +81,7 @@ __global__ void __launch_bounds__(32 * LN_ROWS, 4) embed_ln_kernel(const ItbCtl*
     for (int i = 0; i < LN_MAXV; ++i) {
         const int c = (i * 32 + lane) * 4;
         v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (i < nv && c < d) {
+        if (NVC ? i < NVC : (i < nv && c < d)) {
             const float4 a = *reinterpret_cast<const float4*>(word + (size_t)tok * d + c);
             const float4 e = *reinterpret_cast<const float4*>(pos + (size_t)p * d + c);
             const float4 t = *reinterpret_cast<const float4*>(type + (size_t)lang * d + c);
@@ -87,7 +90,7 @@ __global__ void __launch_bounds__(32 * LN_ROWS, 4) embed_ln_kernel(const ItbCtl*
     }
     // lanes past d hold zeros, which the centred second pass must not count: handled by c < d on load and the exact
     // mean (sum / d); the variance pass subtracts the mean from padded zeros, so d must be a multiple of 128
-    ln_row_write<TA>(v, nv, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, lane);
+    ln_row_write<TA, NVC>(v, nv, d, g, b, eps, x_f32 + (size_t)r * d, x_act + (size_t)r * d, lane);
 }
 
 // Encoder embeddings: every position of the padded source batch at once.  x[b*S + p] = LN(word[tok] + pos[p] + type[lang[b]])
@@ -446,7 +449,13 @@ int itb_embed_ln(int dtype, const itb_ctl* ctl, const int* tokens, const int* tg
     cudaStream_t s = (cudaStream_t)stream;
     const ItbCtl* c = reinterpret_cast<const ItbCtl*>(ctl);
     cudaError_t e;
-    if (dtype == ITB_BF16)
+    if (d == 768 && dtype == ITB_BF16)
+        e = itb_launch(embed_ln_kernel<__nv_bfloat16, 6>, lgrid, lblock, smem, s, c, tokens, tgt_lang, word, pos, type, g, b,
+                       eps, x_f32, (__nv_bfloat16*)x_act, M, beam, d, T_max);
+    else if (d == 768 && dtype == ITB_F16)
+        e = itb_launch(embed_ln_kernel<__half, 6>, lgrid, lblock, smem, s, c, tokens, tgt_lang, word, pos, type, g, b, eps,
+                       x_f32, (__half*)x_act, M, beam, d, T_max);
+    else if (dtype == ITB_BF16)
         e = itb_launch(embed_ln_kernel<__nv_bfloat16>, lgrid, lblock, smem, s, c, tokens, tgt_lang, word, pos, type, g, b,
                        eps, x_f32, (__nv_bfloat16*)x_act, M, beam, d, T_max);
     else if (dtype == ITB_F16)
