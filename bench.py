@@ -82,7 +82,7 @@ class ClockSampler(object):
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", os.environ.get("BENCH_CLOCK_MS", "200")], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -338,9 +338,11 @@ def _dist_max_sum(vals, dev, world):
 
 def _timed(one_pass, steps, warmup, dev, world, sampler=None):
     """W warm-up passes, then K passes bracketed by barrier + synchronize, CUDA events, max over ranks."""
+    import gc
     import torch.distributed as dist
     for _ in range(warmup):
         one_pass()
+    gc.collect()           # start the timed region with a clean heap
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
